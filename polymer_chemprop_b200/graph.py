@@ -1,0 +1,160 @@
+"""Host-side mirror of the reference's graph containers for the encoder hot path.
+
+``MolGraphData`` holds one featurised molecule / polymer (the fields
+``BatchMolGraph.__init__`` reads from a ``MolGraph``:
+chemprop/features/featurization.py:757-813).  ``BatchMolGraph`` is the
+drop-in batch container: same attribute names, same row-0 padding, same
+``get_components()`` 10-tuple (featurization.py:815-846), but assembled with
+vectorised numpy instead of Python list appends.
+
+RDKit featurisation (SMILES -> MolGraph) is out of scope;
+graphs reach this module already featurised.
+"""
+from typing import List, Sequence, Tuple
+
+import numpy as np
+import torch
+
+ATOM_FDIM = 133   # featurization.py:21-43 (101+7+6+5+6+6+1+1)
+BOND_ONLY_FDIM = 14  # featurization.py:229-250
+BOND_FDIM = ATOM_FDIM + BOND_ONLY_FDIM
+
+
+class MolGraphData:
+    """One molecule in the reference's local numbering (atoms/bonds start at 0).
+
+    a2b[a] lists incoming directed bonds of atom ``a`` in append order
+    (featurization.py:467-480); ``b2a[b]`` is the source atom; ``b2revb[b]`` the
+    reverse bond.
+    """
+
+    __slots__ = ("n_atoms", "n_bonds", "f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a",
+                 "b2revb", "degree_of_polym", "overwrite_default_atom_features",
+                 "overwrite_default_bond_features")
+
+    def __init__(self, f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, degree_of_polym=1):
+        self.f_atoms = np.asarray(f_atoms, dtype=np.float32)
+        self.f_bonds = np.asarray(f_bonds, dtype=np.float32)
+        if self.f_atoms.ndim != 2:
+            self.f_atoms = self.f_atoms.reshape(len(w_atoms), ATOM_FDIM if len(w_atoms) == 0 else -1)
+        if self.f_bonds.ndim != 2:
+            self.f_bonds = self.f_bonds.reshape(len(w_bonds), BOND_FDIM if len(w_bonds) == 0 else -1)
+        self.w_atoms = np.asarray(w_atoms, dtype=np.float32)
+        self.w_bonds = np.asarray(w_bonds, dtype=np.float32)
+        self.a2b = [list(map(int, r)) for r in a2b]
+        self.b2a = np.asarray(b2a, dtype=np.int64)
+        self.b2revb = np.asarray(b2revb, dtype=np.int64)
+        self.n_atoms = len(self.w_atoms)
+        self.n_bonds = len(self.w_bonds)
+        self.degree_of_polym = degree_of_polym
+        self.overwrite_default_atom_features = False
+        self.overwrite_default_bond_features = False
+
+    def as_reference_lists(self):
+        """Duck-typed object with plain Python lists, consumable by the *reference's*
+        BatchMolGraph.__init__ (used only by oracle/ scripts and tests)."""
+        import types
+        return types.SimpleNamespace(
+            n_atoms=self.n_atoms, n_bonds=self.n_bonds,
+            f_atoms=self.f_atoms.tolist(), f_bonds=self.f_bonds.tolist(),
+            w_atoms=self.w_atoms.tolist(), w_bonds=self.w_bonds.tolist(),
+            a2b=[list(r) for r in self.a2b], b2a=self.b2a.tolist(), b2revb=self.b2revb.tolist(),
+            degree_of_polym=self.degree_of_polym,
+            overwrite_default_atom_features=False, overwrite_default_bond_features=False)
+
+
+class BatchMolGraph:
+    """Drop-in for chemprop.features.BatchMolGraph (featurization.py:743-875).
+
+    Row 0 of every array is padding; scopes start at 1.  Tensors are created on
+    the CPU exactly like the reference; ``to(device)`` moves them once so the
+    encoder's per-call ``.to(device)`` (mpn.py:84-87) is a no-op afterwards.
+    """
+
+    def __init__(self, mol_graphs: Sequence[MolGraphData]):
+        g0 = mol_graphs[0]
+        self.overwrite_default_atom_features = g0.overwrite_default_atom_features
+        self.overwrite_default_bond_features = g0.overwrite_default_bond_features
+        self.atom_fdim = g0.f_atoms.shape[1] if g0.n_atoms else ATOM_FDIM
+        self.bond_fdim = g0.f_bonds.shape[1] if g0.n_bonds else self.atom_fdim + BOND_ONLY_FDIM
+
+        na = np.fromiter((g.n_atoms for g in mol_graphs), dtype=np.int64, count=len(mol_graphs))
+        nb = np.fromiter((g.n_bonds for g in mol_graphs), dtype=np.int64, count=len(mol_graphs))
+        a_start = 1 + np.concatenate([[0], np.cumsum(na)[:-1]])
+        b_start = 1 + np.concatenate([[0], np.cumsum(nb)[:-1]])
+        self.n_atoms = int(1 + na.sum())
+        self.n_bonds = int(1 + nb.sum())
+        self.a_scope: List[Tuple[int, int]] = [(int(s), int(n)) for s, n in zip(a_start, na)]
+        self.b_scope: List[Tuple[int, int]] = [(int(s), int(n)) for s, n in zip(b_start, nb)]
+        self.degree_of_polym = [g.degree_of_polym for g in mol_graphs]
+
+        f_atoms = np.zeros((self.n_atoms, self.atom_fdim), dtype=np.float32)
+        f_bonds = np.zeros((self.n_bonds, self.bond_fdim), dtype=np.float32)
+        w_atoms = np.zeros(self.n_atoms, dtype=np.float32)
+        w_bonds = np.zeros(self.n_bonds, dtype=np.float32)
+        b2a = np.zeros(self.n_bonds, dtype=np.int64)
+        b2revb = np.zeros(self.n_bonds, dtype=np.int64)
+        max_nb = 1  # max(1, ...) as featurization.py:802-803
+        for g in mol_graphs:
+            for r in g.a2b:
+                if len(r) > max_nb:
+                    max_nb = len(r)
+        self.max_num_bonds = max_nb
+        a2b = np.zeros((self.n_atoms, max_nb), dtype=np.int64)
+        for g, a0, b0 in zip(mol_graphs, a_start, b_start):
+            if g.n_atoms:
+                f_atoms[a0:a0 + g.n_atoms] = g.f_atoms
+                w_atoms[a0:a0 + g.n_atoms] = g.w_atoms
+                for i, r in enumerate(g.a2b):
+                    if r:
+                        a2b[a0 + i, :len(r)] = np.asarray(r, dtype=np.int64) + b0
+            if g.n_bonds:
+                f_bonds[b0:b0 + g.n_bonds] = g.f_bonds
+                w_bonds[b0:b0 + g.n_bonds] = g.w_bonds
+                b2a[b0:b0 + g.n_bonds] = g.b2a + a0
+                b2revb[b0:b0 + g.n_bonds] = g.b2revb + b0
+
+        self.f_atoms = torch.from_numpy(f_atoms)
+        self.f_bonds = torch.from_numpy(f_bonds)
+        self.w_atoms = torch.from_numpy(w_atoms)
+        self.w_bonds = torch.from_numpy(w_bonds)
+        self.a2b = torch.from_numpy(a2b)
+        self.b2a = torch.from_numpy(b2a)
+        self.b2revb = torch.from_numpy(b2revb)
+        self.b2b = None
+        self.a2a = None
+
+    def get_components(self, atom_messages: bool = False):
+        """Same 10-tuple, same order as featurization.py:845-846."""
+        if atom_messages:
+            raise NotImplementedError(
+                "atom_messages=True is not accelerated by the B200 encoder (SURVEY.md section 8a); "
+                "use the reference module for that mode")
+        return (self.f_atoms, self.f_bonds, self.w_atoms, self.w_bonds, self.a2b, self.b2a,
+                self.b2revb, self.a_scope, self.b_scope, self.degree_of_polym)
+
+    def get_a2a(self) -> torch.Tensor:
+        """featurization.py:862-875."""
+        if self.a2a is None:
+            self.a2a = self.b2a[self.a2b]
+        return self.a2a
+
+    def get_b2b(self) -> torch.Tensor:
+        """featurization.py:848-860."""
+        if self.b2b is None:
+            b2b = self.a2b[self.b2a]
+            revmask = (b2b != self.b2revb.unsqueeze(1)).long()
+            self.b2b = b2b * revmask
+        return self.b2b
+
+    def to(self, device, pin: bool = False) -> "BatchMolGraph":
+        """Moves the seven tensors to ``device`` in place (extension over the reference:
+        keeps batches resident so mpn.py:84-87's per-call upload disappears)."""
+        for name in ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a", "b2revb"):
+            t = getattr(self, name)
+            if pin and t.device.type == "cpu":
+                t = t.pin_memory()
+            setattr(self, name, t.to(device, non_blocking=True))
+        if hasattr(self, "_wd_cache"):
+            del self._wd_cache
+        return self

@@ -1,0 +1,48 @@
+"""CPU: the drop-in BatchMolGraph reproduces the reference BatchMolGraph's tensors bit-exactly
+(goldens were built by the reference's own BatchMolGraph.__init__, featurization.py:757-813)."""
+import numpy as np
+import pytest
+import torch
+
+import _golden
+from oracle import make_golden, ref_shim
+from polymer_chemprop_b200 import BatchMolGraph
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_batch_graph_bit_exact_vs_golden(name):
+    build, _cfg = make_golden._cases()[name]
+    bmg = BatchMolGraph(build())
+    ref = _golden.load(name)["components"]
+    got = bmg.get_components()
+    for i in range(7):
+        assert got[i].dtype == ref[i].dtype and got[i].shape == ref[i].shape, i
+        assert torch.equal(got[i], ref[i]), i
+    assert got[7] == ref[7] and got[8] == ref[8]
+    assert [float(x) for x in got[9]] == ref[9]
+
+
+@pytest.mark.skipif(not ref_shim.reference_available(), reason="reference tree absent")
+def test_batch_graph_vs_live_reference():
+    from polymer_chemprop_b200 import synth
+    graphs = synth.make_graphs("copolymer", 5, 123, random_edge_weights=True) + [synth.empty_graph()]
+    ref = ref_shim.load_reference().BatchMolGraph([g.as_reference_lists() for g in graphs])
+    mine = BatchMolGraph(graphs)
+    for a, b in zip(mine.get_components()[:7], ref.get_components()[:7]):
+        assert torch.equal(a, b)
+    assert mine.a_scope == ref.a_scope and mine.b_scope == ref.b_scope
+    assert mine.max_num_bonds == ref.max_num_bonds and mine.n_atoms == ref.n_atoms
+    assert torch.equal(mine.get_a2a(), ref.get_a2a()) and torch.equal(mine.get_b2b(), ref.get_b2b())
+
+
+def test_synthetic_shapes():
+    """copolymer-shaped ~23 atoms / ~66 directed bonds, K 7-8, self-loop pairs."""
+    from polymer_chemprop_b200 import synth
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 200, 0))
+    assert 20 < (bmg.n_atoms - 1) / 200 < 26 and 58 < (bmg.n_bonds - 1) / 200 < 72
+    assert bmg.max_num_bonds in (7, 8)
+    dst = bmg.b2a[bmg.b2revb]
+    assert int((dst[1:] == bmg.b2a[1:]).sum()) == 200 * 8       # 4 self pairs x 2 directed bonds
+    assert torch.equal(bmg.f_bonds[:, :133], bmg.f_atoms[bmg.b2a])
+    q = BatchMolGraph(synth.make_graphs("qm9", 200, 0))
+    assert q.max_num_bonds <= 4 and 7 <= (q.n_atoms - 1) / 200 <= 9

@@ -1,0 +1,52 @@
+"""CPU: the oracle restatements reproduce the reference's golden outputs and gradients."""
+import numpy as np
+import pytest
+import torch
+
+import _golden
+from oracle import mpn_explicit, mpn_oracle
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_oracle_matches_reference_golden(name):
+    g = _golden.load(name)
+    weights = {k: v for k, v in g["params"].items() if k != "cached_zero_vector"}
+    out, grads = mpn_oracle.encoder_forward_backward(g["components"], weights, g["d_out"],
+                                                     **_golden.oracle_cfg(g["cfg"]))
+    # same op sequence on the same torch build: expect (near) bit equality
+    assert _golden.rel_err(out, g["out"]) <= 1e-6
+    assert set(grads) == set(g["grads"])
+    for k in grads:
+        assert _golden.rel_err(grads[k], g["grads"][k]) <= 1e-5, k
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_explicit_backward_matches_reference_golden(name):
+    g = _golden.load(name)
+    weights = {k: v.numpy() for k, v in g["params"].items() if k != "cached_zero_vector"}
+    comps = g["components"]
+    out, grads = mpn_explicit.forward_backward(comps, weights, g["d_out"].numpy(),
+                                               **_golden.oracle_cfg(g["cfg"]))
+    assert _golden.rel_err(out, g["out"]) <= 2e-6     # f64 vs reference f32
+    for k, ref in g["grads"].items():
+        assert _golden.rel_err(grads[k], ref) <= 2e-5, k
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_csr_oracle_properties(name):
+    """Index oracle invariants: every real bond appears once in in_idx and once
+    in out_idx; in-list order equals the padded row's non-zero prefix; dst is consistent."""
+    f_atoms, f_bonds, w_a, w_b, a2b, b2a, b2revb, *_ = _golden.load(name)["components"]
+    in_ptr, in_idx, out_ptr, out_idx, dst = mpn_oracle.csr_from_a2b(a2b.tolist(), b2a.tolist(), b2revb.tolist())
+    n_b = b2a.numel()
+    assert sorted(in_idx.tolist()) == list(range(1, n_b))
+    assert sorted(out_idx.tolist()) == list(range(1, n_b))
+    for a in range(a2b.shape[0]):
+        row = [b for b in a2b[a].tolist() if b]
+        assert in_idx[in_ptr[a]:in_ptr[a + 1]].tolist() == row
+        assert a2b[a].tolist()[:len(row)] == row          # zeros only as a suffix
+        for b in row:
+            assert dst[b] == a
+        outs = out_idx[out_ptr[a]:out_ptr[a + 1]].tolist()
+        assert outs == sorted(outs) and all(int(b2a[b]) == a for b in outs)
+    assert np.array_equal(b2revb[b2revb].numpy(), np.arange(n_b))
