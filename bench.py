@@ -1,0 +1,369 @@
+"""Benchmark of the wD-MPNN encoder hot path (BASELINE.json metric: encoder graphs/sec, fwd+bwd,
+h=300, d=3, synthetic copolymer-shaped graphs, batch 4096 per GPU).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A step = MPN.forward(batch) + out.backward(d_out) on one batch (+ one NCCL all-reduce of the
+flat gradient when N > 1).  Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "wD-MPNN encoder graphs/sec (fwd+bwd) at h=300,d=3"
+UNIT = "graphs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=4096, help="graphs per GPU per step")
+    ap.add_argument("--hidden", type=int, default=300)
+    ap.add_argument("--depth", type=int, default=3)
+    ap.add_argument("--kind", default="copolymer", choices=["copolymer", "qm9"])
+    ap.add_argument("--math", default=os.environ.get("WDMPNN_MATH", "fp32"), choices=["fp32", "tf32"])
+    ap.add_argument("--cpu-sample", type=int, default=512, help="graphs in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def make_model_args(a, device):
+    return types.SimpleNamespace(
+        hidden_size=a.hidden, depth=a.depth, bias=False, dropout=0.0, activation="ReLU",
+        atom_messages=False, undirected=False, aggregation="mean", aggregation_norm=100,
+        atom_descriptors=None, atom_descriptors_size=0, device=device, mpn_shared=False,
+        number_of_molecules=1, features_only=False, use_input_features=False,
+        overwrite_default_atom_features=False, overwrite_default_bond_features=False,
+        wd_math_mode=a.math)
+
+
+def init_weights(model, seed=0):
+    """initialize_weights semantics (chemprop/nn_utils.py:102-112): xavier-normal matrices, zero vectors."""
+    torch.manual_seed(seed)
+    for p in model.parameters():
+        if not p.requires_grad:
+            continue
+        if p.dim() == 1:
+            torch.nn.init.constant_(p, 0)
+        else:
+            torch.nn.init.xavier_normal_(p)
+
+
+def workload_name(a):
+    return (f"synthetic {a.kind}-shaped graphs, batch {a.batch}/GPU, hidden {a.hidden}, depth {a.depth} "
+            f"(BASELINE.json configs[1])")
+
+
+# --------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port of the reference's op sequence on the host cores
+# --------------------------------------------------------------------------------------------
+def cpu_baseline(graphs, a, budget_s=12.0, max_steps=10, warmup=1):
+    from oracle import mpn_oracle
+    from polymer_chemprop_b200 import BatchMolGraph
+    n = min(a.cpu_sample, len(graphs))
+    bmg = BatchMolGraph(graphs[:n])
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    h, fa, fb = a.hidden, bmg.atom_fdim, bmg.bond_fdim
+    gen = torch.Generator().manual_seed(0)
+    weights = {"W_i.weight": torch.randn(h, fb, generator=gen) * 0.07,
+               "W_h.weight": torch.randn(h, h, generator=gen) * 0.06,
+               "W_o.weight": torch.randn(h, fa + h, generator=gen) * 0.05,
+               "W_o.bias": torch.zeros(h)}
+    d_out = torch.randn(n, h, generator=gen)
+    comps = bmg.get_components()
+    times = []
+    for i in range(warmup + max_steps):
+        t0 = time.perf_counter()
+        mpn_oracle.encoder_forward_backward(comps, weights, d_out, depth=a.depth)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+            if sum(times) > budget_s:
+                break
+    ms = 1e3 * float(np.mean(times))
+    return {"value": n / (ms * 1e-3), "unit": UNIT, "cores": cores, "kind": "port",
+            "threads": torch.get_num_threads(), "ms_per_step": ms, "steps": len(times),
+            "sample": f"first {n} graphs of the rank-0 batch per step, reference op sequence "
+                      f"(oracle/mpn_oracle.py) on torch CPU fp32; cost is super-linear in batch "
+                      f"(per-molecule readout backward), so larger batches are slower per graph"}
+
+
+def run_reference(a):
+    """--impl reference: the reference's own CPU implementation of the path.  /root/reference is not on
+    the GPU box and it is pure Python, so the timed code is the oracle port of its op sequence."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from polymer_chemprop_b200 import synth
+    graphs = synth.make_graphs(a.kind, a.cpu_sample, seed=0)
+    steps = max(1, a.steps)
+    cb = cpu_baseline(graphs, a, budget_s=150.0, max_steps=steps, warmup=max(1, min(a.warmup, 2)))
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
+            "steps": cb["steps"], "warmup": max(1, min(a.warmup, 2)), "ms_per_step": cb["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": workload_name(a), "parallelism": "host cores only"},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md "clocks line")
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# algorithmic bytes per launch of each kernel category (DESIGN.md "Kernels and rooflines")
+# --------------------------------------------------------------------------------------------
+def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d):
+    P, Q = 4.0 * Nb * h, 4.0 * Na * h            # one [N_b,h] / [N_a,h] fp32 pass
+    steps = max(d - 1, 1)
+    depth_total = (2 * P + Q) + (d - 2) * (3 * P + Q) if d > 1 else 0.0   # t=1 reads I once
+    return {
+        "input_proj": 4.0 * Nb * Fb + P + 4.0 * h * Fb,
+        "aggregate": P + Q + 12.0 * Nb + 4.0 * Na,
+        "depth_step": depth_total / steps + 8.0 * Nb + 4.0 * h * h,
+        "atom_update": 4.0 * Na * Fa + 2 * Q + 4.0 * h * (Fa + h),
+        "readout": (2 * Q + 4.0 * G * h) * 0.5 + (Q + 4.0 * G * h) * 0.5,   # bwd (H, dZo, d_out) / fwd (H, out)
+        "msg_grad": 4 * P + Q + 12.0 * Nb,        # dS, Y, dZ, dI + gathered dA rows
+        "dw": 2 * P,                              # dZ and the recomputed S / features (per dW launch)
+        "dx": 2 * P + 4.0 * h * h,
+        "scatter": P + Q + 8.0 * Nb,
+        "misc": 0.0,
+    }
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            p = json.load(open(path))
+            return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class HostGraph:
+    """A fresh, uncached batch object over pinned HOST tensors (the reference's calling convention:
+    get_components() returns CPU tensors, mpn.py:81-87) -- used by the end-to-end leg."""
+
+    def __init__(self, comps):
+        self._c = comps
+
+    def get_components(self, atom_messages=False):
+        return self._c
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        return run_reference(a)
+    import torch.distributed as dist
+    from polymer_chemprop_b200 import MPN, BatchMolGraph, DeviceGraph, _capi, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback for the hot path)")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    # per-rank shard of the global batch: independent graphs, no data-path collective (weak scaling)
+    graphs = synth.make_graphs(a.kind, a.batch, seed=rank)
+    bmg = BatchMolGraph(graphs)
+    model = MPN(make_model_args(a, dev), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(dev)
+    init_weights(model)
+    params = [p for p in model.parameters() if p.requires_grad]
+    dg = DeviceGraph.get(bmg, dev)                       # inputs resident in HBM before timing
+    Na, Nb, G = dg.n_atoms, dg.n_bonds, dg.n_mols
+    d_out = torch.randn(G, a.hidden, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
+
+    def step():
+        for p in params:
+            p.grad = None
+        out = model([bmg])
+        out.backward(d_out)
+        if world > 1:                                    # data-parallel gradient all-reduce (one flat buffer)
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat)
+            flat.div_(world)
+        return out
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    sync_all()
+    lib = _capi.lib()
+    lib.wd_profile_reset()
+    lib.wd_profile_enable(1)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = _capi.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    sync_all()
+    clocks = sampler.stop() if rank == 0 else None
+    lib.wd_profile_enable(0)
+    launches = _capi.launch_count() - n0
+    ms_total = e0.elapsed_time(e1)
+    prof = _capi.profile_read()
+    lib.wd_profile_reset()
+    t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / a.steps
+    value = world * G / (ms_step * 1e-3)
+
+    # ---- end to end: pinned host tensors -> H2D -> CSR build -> fwd+bwd -> D2H of the encoder output
+    e2e = None
+    if not a.no_e2e:
+        comps = bmg.get_components()
+        pinned = tuple(x.pin_memory() for x in comps[:7]) + tuple(comps[7:])
+        h2d = sum(x.numel() * x.element_size() for x in pinned[:7]) + G * 12
+        host_out = torch.empty(G, a.hidden).pin_memory()
+        d2h = host_out.numel() * 4
+
+        def e2e_step():
+            for p in params:
+                p.grad = None
+            out = model([HostGraph(pinned)])
+            out.backward(d_out)
+            if world > 1:
+                flat = torch.cat([p.grad.reshape(-1) for p in params])
+                dist.all_reduce(flat)
+            host_out.copy_(out.detach(), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        for _ in range(3):
+            e2e_step()
+        sync_all()
+        k = max(3, min(a.steps, 10))
+        t0 = time.perf_counter()
+        for _ in range(k):
+            e2e_step()
+        sync_all()
+        te = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": k,
+               "api": "MPN.forward([batch with pinned CPU tensors]) + backward + out.cpu()"}
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        alg = algorithmic_bytes(Na, Nb, G, a.hidden, bmg.atom_fdim, bmg.bond_fdim, a.depth)
+        kernels = {}
+        gpu_ms = sum(ms for ms, _n in prof.values())
+        for name, (ms, n) in prof.items():
+            if n == 0:
+                continue
+            per = ms / n
+            gbs = alg[name] / (per * 1e-3) / 1e9 if alg[name] else None
+            kernels[name] = {"launches_per_step": n / a.steps, "ms_per_launch": per,
+                             "share_of_gpu_time": ms / gpu_ms if gpu_ms else None,
+                             "alg_bytes_per_launch": alg[name], "achieved_gbs": gbs,
+                             "frac_of_hbm_peak": gbs / peak if gbs else None}
+        dom = max((k for k in kernels if k != "misc"), key=lambda k: kernels[k]["share_of_gpu_time"])
+        roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
+                "unit": "GB/s", "frac": kernels[dom]["frac_of_hbm_peak"], "traffic": None,
+                "peak_source": peak_src, "ms_per_launch": kernels[dom]["ms_per_launch"],
+                "alg_bytes_per_launch": alg[dom]}
+        step_bytes = sum(alg[k] * v["launches_per_step"] for k, v in kernels.items())
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+                "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32" if a.math == "fp32" else "tf32",
+                "data": "synthetic",
+                "config": {"workload": workload_name(a), "global_batch": world * G, "n_atoms": Na, "n_bonds": Nb,
+                           "parallelism": f"dp{world}" if world > 1 else "single GPU",
+                           "l2": "per-step working set (workspace >= 2 GB at batch 4096) exceeds the 126 MB L2",
+                           "math_mode": a.math},
+                "edge_msgs_per_s": world * (Nb - 1) * max(a.depth - 1, 0) / (ms_step * 1e-3),
+                "roofline": roof, "kernels": kernels,
+                "step_hbm": {"alg_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,
+                             "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
+                "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e}
+        if not a.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(graphs, a)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

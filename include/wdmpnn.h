@@ -1,0 +1,170 @@
+/*
+ * wdmpnn.h -- C ABI of the B200 (sm_100a) wD-MPNN encoder hot path.
+ *
+ * Drop-in boundary for chemprop/models/mpn.py (MPNEncoder.forward :66-173 and its autograd
+ * backward).  The reference is pure Python/PyTorch and has no FFI of its own; these entry
+ * points are what a binding for that path binds (ctypes stub: INTEGRATION.md, shipped binding:
+ * polymer_chemprop_b200/_capi.py).  Plain pointers and sizes only -- no torch / C++ types.
+ *
+ * Ownership: the caller owns every buffer (inputs, outputs, gradients, workspace).  The library
+ * allocates nothing persistent and keeps no state except a thread-local error string and a
+ * launch counter.  All pointers are DEVICE pointers unless stated otherwise.  All kernels are
+ * enqueued on `stream` (a cudaStream_t passed as void*); no call synchronises except
+ * wd_csr_build_check().  Return value: 0 on success, negative WD_ERR_* otherwise, message via
+ * wd_last_error().
+ */
+#ifndef WDMPNN_H_
+#define WDMPNN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WD_OK 0
+#define WD_ERR_INVALID_ARG (-1)
+#define WD_ERR_CUDA (-2)
+#define WD_ERR_UNSUPPORTED (-3)
+#define WD_ERR_GRAPH (-4) /* BatchMolGraph invariants violated (see wd_csr_build_check) */
+
+/* activation: chemprop/nn_utils.py:70-99 (PReLU has a learned slope and is not supported) */
+enum { WD_ACT_RELU = 0, WD_ACT_LEAKY_RELU = 1, WD_ACT_TANH = 2, WD_ACT_SELU = 3, WD_ACT_ELU = 4 };
+/* aggregation: chemprop/models/mpn.py:158-163 */
+enum { WD_AGG_MEAN = 0, WD_AGG_SUM = 1, WD_AGG_NORM = 2 };
+/* math_mode: arithmetic of the h x h / F x h contractions.
+ *   FP32  : CUDA-core FFMA, fp32 accumulate              (parity <= 1e-5 relative)
+ *   TF32  : tcgen05.mma kind::tf32, fp32 accumulate in TMEM (parity <= 1e-3 relative) */
+enum { WD_MATH_FP32 = 0, WD_MATH_TF32 = 1 };
+
+/* Encoder configuration == the TrainArgs fields MPNEncoder.__init__ reads (mpn.py:24-35). */
+typedef struct WdConfig {
+  int32_t hidden_size;     /* args.hidden_size                                   */
+  int32_t atom_fdim;       /* F_a (133 by default)                               */
+  int32_t bond_fdim;       /* F_b = F_a + 14 (147 by default)                    */
+  int32_t depth;           /* args.depth  (>= 1; depth-1 message-passing steps)  */
+  int32_t activation;      /* WD_ACT_*                                           */
+  int32_t aggregation;     /* WD_AGG_*                                           */
+  int32_t undirected;      /* args.undirected                                    */
+  int32_t bias;            /* args.bias: W_i / W_h carry a bias                  */
+  int32_t math_mode;       /* WD_MATH_*                                          */
+  float aggregation_norm;  /* args.aggregation_norm                              */
+} WdConfig;
+
+/* One BatchMolGraph on the device: get_components() tensors (featurization.py:815-846) plus the
+ * int32 CSR arrays produced by wd_csr_build.  Row 0 of every per-atom / per-bond array is the
+ * reference's padding row. */
+typedef struct WdGraph {
+  int64_t n_atoms;        /* N_a incl. padding row                  */
+  int64_t n_bonds;        /* N_b incl. padding row                  */
+  int64_t n_mols;         /* G = len(a_scope)                       */
+  const float* f_atoms;   /* [N_a, F_a] row-major                   */
+  const float* f_bonds;   /* [N_b, F_b] row-major                   */
+  const float* w_atoms;   /* [N_a]                                  */
+  const float* w_bonds;   /* [N_b]                                  */
+  const int32_t* in_ptr;  /* [N_a+1] CSR of incoming bonds per atom (== out_ptr, see below) */
+  const int32_t* in_idx;  /* [N_b-1] non-zero prefix of each a2b row, reference order        */
+  const int32_t* out_idx; /* [N_b-1] bonds grouped by source atom b2a[b], ascending bond id  */
+  const int32_t* src;     /* [N_b] int32 copy of b2a                */
+  const int32_t* rev;     /* [N_b] int32 copy of b2revb             */
+  const int32_t* dst;     /* [N_b] dst[b] = atom whose a2b row holds b (== b2a[b2revb[b]])   */
+  const int32_t* mol_of;  /* [N_a] molecule index of each atom, -1 if in no a_scope          */
+  const int32_t* a_start; /* [G] a_scope starts                     */
+  const int32_t* a_size;  /* [G] a_scope sizes                      */
+  const float* dop;       /* [G] degree_of_polym                    */
+} WdGraph;
+
+/* nn.Linear layout [out, in] row-major, exactly the reference's parameters (mpn.py:47-57).
+ * b_i / b_h may be NULL when cfg.bias == 0. */
+typedef struct WdWeights {
+  const float* W_i; /* [h, F_b]      */
+  const float* b_i; /* [h] or NULL   */
+  const float* W_h; /* [h, h]        */
+  const float* b_h; /* [h] or NULL   */
+  const float* W_o; /* [h, F_a + h]  */
+  const float* b_o; /* [h]           */
+} WdWeights;
+
+/* Gradients, same shapes as WdWeights; each buffer is OVERWRITTEN (not accumulated). */
+typedef struct WdGrads {
+  float* dW_i;
+  float* db_i;
+  float* dW_h;
+  float* db_h;
+  float* dW_o;
+  float* db_o;
+} WdGrads;
+
+/* Rebuilds BatchMolGraph's padded a2b [N_a, K] int64 (featurization.py:805) into CSR on the
+ * device and narrows b2a / b2revb to int32.  Because every out-edge of an atom is the reverse
+ * of one of its in-edges, out-degree == in-degree and `in_ptr` also delimits `out_idx`.
+ * a_start / a_size are DEVICE int32 [G]; mol_of [N_a] is filled from them.
+ * `flags` is a DEVICE int32[4] written by the kernels: [0] number of invariant violations
+ * (bond id out of range, bond listed in 0 or >1 rows, dst != b2a[b2revb], b2revb not an
+ * involution, scope out of range), [1] max in-degree seen, [2..3] reserved. */
+int wd_csr_build(const int64_t* a2b, int64_t n_atoms, int64_t max_num_bonds, const int64_t* b2a,
+                 const int64_t* b2revb, int64_t n_bonds, const int32_t* a_start,
+                 const int32_t* a_size, int64_t n_mols, int32_t* in_ptr, int32_t* in_idx,
+                 int32_t* out_idx, int32_t* src, int32_t* rev, int32_t* dst, int32_t* mol_of,
+                 int32_t* flags, void* stream);
+
+/* Synchronises `stream`, reads `flags` back and returns WD_ERR_GRAPH if flags[0] != 0. */
+int wd_csr_build_check(const int32_t* flags, void* stream);
+
+/* Bytes of caller-provided workspace.  The forward pass stores there what the backward pass
+ * re-reads (I, M_t, A_t, H) plus scratch; pass the same buffer, untouched, to the backward. */
+size_t wd_workspace_bytes(const WdConfig* cfg, int64_t n_atoms, int64_t n_bonds, int64_t n_mols);
+
+/* out[G, h] = MPNEncoder.forward(graph)  (mpn.py:92-171, bond messages, dropout 0). */
+int wd_encoder_forward(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,
+                       void* workspace, size_t workspace_bytes, float* out, void* stream);
+
+/* Gradients of sum(out * d_out) w.r.t. the weights; deterministic (no atomics). */
+int wd_encoder_backward(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,
+                        void* workspace, size_t workspace_bytes, const float* d_out,
+                        const WdGrads* grads, void* stream);
+
+/* HOST-buffer entry point (the reference's own calling convention: get_components() hands CPU
+ * tensors to MPNEncoder.forward, mpn.py:81-87).  All graph pointers here are HOST pointers;
+ * a_scope is [G,2] int64 (start,size) pairs, dop double[G].  Uploads, builds the CSR, runs
+ * forward (+ backward when d_out != NULL) and copies out[G,h] (and gradients) back to the host.
+ * Device memory is allocated per call with cudaMallocAsync on `stream`. */
+int wd_encoder_host(const float* f_atoms, const float* f_bonds, const float* w_atoms,
+                    const float* w_bonds, const int64_t* a2b, const int64_t* b2a,
+                    const int64_t* b2revb, const int64_t* a_scope, const double* dop,
+                    int64_t n_atoms, int64_t n_bonds, int64_t max_num_bonds, int64_t n_mols,
+                    const WdWeights* host_weights, const WdConfig* cfg, float* out,
+                    const float* d_out, const WdGrads* host_grads, void* stream);
+
+/* Per-category device timing of this library's own launches, measured with CUDA events recorded
+ * on the launching stream around each kernel (for bench.py's roofline line).  Off by default. */
+enum {
+  WD_PROF_INPUT_PROJ = 0,  /* I = W_i(f_bonds)                                   mpn.py:96      */
+  WD_PROF_AGGREGATE = 1,   /* CSR gather a_message                               mpn.py:112-118 */
+  WD_PROF_DEPTH_STEP = 2,  /* act(input + W_h(a_message[b2a] - message[b2revb]))  mpn.py:119-123 */
+  WD_PROF_ATOM_UPDATE = 3, /* act(W_o([f_atoms, a_message]))                     mpn.py:132-133 */
+  WD_PROF_READOUT = 4,     /* weighted per-molecule readout fwd+bwd              mpn.py:146-171 */
+  WD_PROF_MSG_GRAD = 5,    /* backward message gradient + activation mask                        */
+  WD_PROF_DW = 6,          /* weight-gradient contractions dW_h / dW_i / dW_o / biases           */
+  WD_PROF_DX = 7,          /* dS = dZ W_h and dA_d = dZo W_o[:, F_a:]                            */
+  WD_PROF_SCATTER = 8,     /* transpose-CSR scatter of dS onto source atoms                      */
+  WD_PROF_MISC = 9,        /* CSR build, symmetrisation, everything else                         */
+  WD_PROF_NUM = 10
+};
+void wd_profile_enable(int on); /* on != 0: record events around every launch from now on      */
+void wd_profile_reset(void);    /* forget recorded launches (keeps the event pool)              */
+/* Synchronises the recorded events and returns total milliseconds and launch count of category. */
+int wd_profile_read(int category, double* total_ms, int64_t* launches);
+
+/* Thread-local message of the last failing call on this thread. */
+const char* wd_last_error(void);
+/* Kernel launches issued by this library since load (for bench.py's gpu_launches). */
+int64_t wd_launch_count(void);
+/* ABI version of this header. */
+int wd_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WDMPNN_H_ */

@@ -1,0 +1,127 @@
+"""ctypes binding of include/wdmpnn.h (the C-ABI of libwdmpnn.so).
+
+There is no CPU fallback: if the library is missing or the device is not CUDA the
+callers raise.  torch is used only for device memory and the current stream.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libwdmpnn.so")
+
+WD_OK, WD_ERR_INVALID_ARG, WD_ERR_CUDA, WD_ERR_UNSUPPORTED, WD_ERR_GRAPH = 0, -1, -2, -3, -4
+ACTIVATIONS = {"ReLU": 0, "LeakyReLU": 1, "tanh": 2, "SELU": 3, "ELU": 4}
+AGGREGATIONS = {"mean": 0, "sum": 1, "norm": 2}
+MATH_MODES = {"fp32": 0, "tf32": 1}
+
+_f32p, _i32p, _i64p = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int64)
+
+
+class WdConfig(C.Structure):
+    _fields_ = [("hidden_size", C.c_int32), ("atom_fdim", C.c_int32), ("bond_fdim", C.c_int32),
+                ("depth", C.c_int32), ("activation", C.c_int32), ("aggregation", C.c_int32),
+                ("undirected", C.c_int32), ("bias", C.c_int32), ("math_mode", C.c_int32),
+                ("aggregation_norm", C.c_float)]
+
+
+class WdGraph(C.Structure):
+    _fields_ = [("n_atoms", C.c_int64), ("n_bonds", C.c_int64), ("n_mols", C.c_int64),
+                ("f_atoms", C.c_void_p), ("f_bonds", C.c_void_p), ("w_atoms", C.c_void_p),
+                ("w_bonds", C.c_void_p), ("in_ptr", C.c_void_p), ("in_idx", C.c_void_p),
+                ("out_idx", C.c_void_p), ("src", C.c_void_p), ("rev", C.c_void_p), ("dst", C.c_void_p),
+                ("mol_of", C.c_void_p), ("a_start", C.c_void_p), ("a_size", C.c_void_p),
+                ("dop", C.c_void_p)]
+
+
+class WdWeights(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("W_i", "b_i", "W_h", "b_h", "W_o", "b_o")]
+
+
+class WdGrads(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("dW_i", "db_i", "dW_h", "db_h", "dW_o", "db_o")]
+
+
+EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_workspace_bytes", "wd_encoder_forward",
+           "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
+           "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read")
+PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
+                   "dx", "scatter", "misc")
+
+_lib = None
+
+
+def lib():
+    """Loads libwdmpnn.so (building it in-tree if the sources are newer)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH) or os.environ.get("WDMPNN_REBUILD"):
+        from . import build as _build
+        _build.build()
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -m polymer_chemprop_b200.build` "
+                           "(there is no CPU fallback for the encoder hot path)")
+    L = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    L.wd_csr_build.argtypes = [vp, C.c_int64, C.c_int64, vp, vp, C.c_int64, vp, vp, C.c_int64] + [vp] * 8 + [vp]
+    L.wd_csr_build.restype = C.c_int
+    L.wd_csr_build_check.argtypes = [vp, vp]
+    L.wd_csr_build_check.restype = C.c_int
+    L.wd_workspace_bytes.argtypes = [C.POINTER(WdConfig), C.c_int64, C.c_int64, C.c_int64]
+    L.wd_workspace_bytes.restype = C.c_size_t
+    L.wd_encoder_forward.argtypes = [C.POINTER(WdGraph), C.POINTER(WdWeights), C.POINTER(WdConfig), vp,
+                                     C.c_size_t, vp, vp]
+    L.wd_encoder_forward.restype = C.c_int
+    L.wd_encoder_backward.argtypes = [C.POINTER(WdGraph), C.POINTER(WdWeights), C.POINTER(WdConfig), vp,
+                                      C.c_size_t, vp, C.POINTER(WdGrads), vp]
+    L.wd_encoder_backward.restype = C.c_int
+    L.wd_encoder_host.argtypes = [vp] * 9 + [C.c_int64] * 4 + [C.POINTER(WdWeights), C.POINTER(WdConfig), vp, vp,
+                                                               C.POINTER(WdGrads), vp]
+    L.wd_encoder_host.restype = C.c_int
+    L.wd_last_error.restype = C.c_char_p
+    L.wd_launch_count.restype = C.c_int64
+    L.wd_abi_version.restype = C.c_int
+    L.wd_profile_enable.argtypes = [C.c_int]
+    L.wd_profile_enable.restype = None
+    L.wd_profile_reset.restype = None
+    L.wd_profile_read.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.wd_profile_read.restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc: int):
+    """Maps the C error convention onto the reference's Python exceptions (mpn.py raises
+    ValueError / NotImplementedError; everything else is a RuntimeError)."""
+    if rc == WD_OK:
+        return
+    msg = lib().wd_last_error().decode("utf-8", "replace")
+    if rc == WD_ERR_UNSUPPORTED:
+        raise NotImplementedError(msg)
+    if rc in (WD_ERR_INVALID_ARG, WD_ERR_GRAPH):
+        raise ValueError(msg)
+    raise RuntimeError(f"wdmpnn error {rc}: {msg}")
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def current_stream(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def launch_count() -> int:
+    return int(lib().wd_launch_count())
+
+
+def profile_read():
+    """{category: (total_ms, launches)} of the launches recorded since the last reset."""
+    out = {}
+    for i, name in enumerate(PROF_CATEGORIES):
+        ms, n = C.c_double(0.0), C.c_int64(0)
+        check(lib().wd_profile_read(i, C.byref(ms), C.byref(n)))
+        out[name] = (ms.value, n.value)
+    return out

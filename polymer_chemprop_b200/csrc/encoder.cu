@@ -1,0 +1,323 @@
+// C-ABI entry points and kernel sequencing of the wD-MPNN encoder (include/wdmpnn.h).
+// Forward  == chemprop/models/mpn.py:92-171 (bond messages, dropout 0).
+// Backward == autograd of the same, restated as deterministic CSR kernels.
+#include "common.cuh"
+#include "graph_kernels.cuh"
+#include "operands.cuh"
+#include "simt_gemm.cuh"
+
+namespace wd {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+namespace {
+
+// ---- workspace layout (in floats; every section 256-byte aligned) --------------------------
+struct Layout {
+  int ldh;                 // row stride of every [*, h] activation buffer (h rounded up to 4)
+  int64_t szB, szA;        // floats per [N_b, ldh] / [N_a, ldh] buffer
+  int64_t I, M, Agg, H, mscale, U, dZ, dS, dI, dA, dZo, partials, total;
+  int Z;                   // row chunks of the weight-gradient contractions
+  float* p(void* ws, int64_t off) const { return reinterpret_cast<float*>(ws) + off; }
+};
+
+int dw_chunks(int64_t rows, int n1, int n2) {
+  int64_t tiles = ceil_div(n1, DW_BM) * ceil_div(n2, DW_BN);
+  int64_t z = ceil_div(4 * kNumSMs, tiles);
+  z = std::min<int64_t>(z, std::max<int64_t>(1, rows / 256));
+  return (int)std::max<int64_t>(1, std::min<int64_t>(z, 64));
+}
+
+Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
+  Layout L;
+  const int h = c.hidden_size;
+  L.ldh = (int)round_up(h, 4);
+  L.szB = round_up(Nb * L.ldh, 64);
+  L.szA = round_up(Na * L.ldh, 64);
+  int64_t off = 0;
+  auto take = [&](int64_t n) { int64_t o = off; off += round_up(n, 64); return o; };
+  L.I = take(L.szB);
+  L.M = take((int64_t)std::max(0, c.depth - 1) * L.szB);
+  L.Agg = take((int64_t)c.depth * L.szA);
+  L.H = take(L.szA);
+  L.mscale = take(G);
+  L.U = take(c.undirected ? L.szB : 0);
+  L.dZ = take(L.szB);
+  L.dS = take(L.szB);
+  L.dI = take(L.szB);
+  L.dA = take(L.szA);
+  L.dZo = take(L.szA);
+  const int Fo = c.atom_fdim + h;
+  L.Z = std::max(std::max(dw_chunks(Nb, h, h), dw_chunks(Nb, h, c.bond_fdim)), dw_chunks(Na, h, Fo));
+  int64_t pw = std::max<int64_t>((int64_t)std::max(1, c.depth - 1) * h * h,
+                                 (int64_t)h * std::max(Fo, c.bond_fdim));
+  L.partials = take((int64_t)L.Z * pw + (int64_t)L.Z * h);
+  L.total = off;
+  return L;
+}
+
+int check_cfg(const WdConfig* c) {
+  if (!c) return fail(WD_ERR_INVALID_ARG, "cfg is NULL");
+  if (c->hidden_size < 1 || c->atom_fdim < 1 || c->bond_fdim < 1 || c->depth < 1)
+    return fail(WD_ERR_INVALID_ARG, "hidden_size/atom_fdim/bond_fdim/depth must be >= 1");
+  if (c->activation < WD_ACT_RELU || c->activation > WD_ACT_ELU)
+    return fail(WD_ERR_UNSUPPORTED, "activation %d not supported (ReLU, LeakyReLU, tanh, SELU, ELU)", c->activation);
+  if (c->aggregation < WD_AGG_MEAN || c->aggregation > WD_AGG_NORM)
+    return fail(WD_ERR_INVALID_ARG, "aggregation %d unknown", c->aggregation);
+  if (c->math_mode != WD_MATH_FP32 && c->math_mode != WD_MATH_TF32)
+    return fail(WD_ERR_INVALID_ARG, "math_mode %d unknown", c->math_mode);
+  return WD_OK;
+}
+
+int check_graph(const WdGraph* g, const WdWeights* w, const WdConfig* c) {
+  if (!g || !w) return fail(WD_ERR_INVALID_ARG, "graph/weights is NULL");
+  if (g->n_atoms < 1 || g->n_bonds < 1 || g->n_mols < 0)
+    return fail(WD_ERR_INVALID_ARG, "graph sizes invalid (n_atoms=%lld n_bonds=%lld n_mols=%lld)",
+                (long long)g->n_atoms, (long long)g->n_bonds, (long long)g->n_mols);
+  if (!g->f_atoms || !g->f_bonds || !g->w_atoms || !g->w_bonds || !g->in_ptr || !g->src || !g->rev ||
+      !g->dst || !g->mol_of || (g->n_bonds > 1 && (!g->in_idx || !g->out_idx)) ||
+      (g->n_mols > 0 && (!g->a_start || !g->a_size || !g->dop)))
+    return fail(WD_ERR_INVALID_ARG, "graph has NULL device pointers");
+  if (!w->W_i || !w->W_h || !w->W_o || !w->b_o || (c->bias && (!w->b_i || !w->b_h)))
+    return fail(WD_ERR_INVALID_ARG, "weights have NULL device pointers");
+  return WD_OK;
+}
+
+inline int grid1d(int64_t n, int block = 256) { return (int)ceil_div(std::max<int64_t>(n, 1), block); }
+
+// ---- contraction dispatch: FP32 SIMT today; TF32 tcgen05 kernels plug in here -------------
+template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
+int gemm(const WdConfig& c, cudaStream_t s, const AOperand& A, const float* W, int ldb, const float* bias,
+         const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K) {
+  dim3 grid((unsigned)ceil_div(M, SG_BM), (unsigned)ceil_div(std::max(N, ldc), SG_BN));
+  WD_LAUNCH((k_simt_gemm<AMODE, BMODE, EPI, ACT, PREACT>), grid, SG_THREADS, 0, s, A, W, ldb, bias, R, ldr,
+            C, ldc, M, N, K);
+  return WD_OK;
+}
+
+// P[z_off .. z_off+Z) <- partial X^T Y over row chunks
+template <int YMODE, int ACT, bool PREACT>
+int dw_partial(cudaStream_t s, const float* X, int ldx, const AOperand& Y, float* P, int64_t R, int N1,
+               int N2, int Z) {
+  int64_t rpc = round_up(ceil_div(R, Z), DW_BK);
+  dim3 grid((unsigned)ceil_div(N2, DW_BN), (unsigned)ceil_div(N1, DW_BM), (unsigned)Z);
+  WD_LAUNCH((k_simt_dw<YMODE, ACT, PREACT>), grid, DW_THREADS, 0, s, X, ldx, Y, P, R, N1, N2, rpc);
+  return WD_OK;
+}
+
+int reduce_partials(cudaStream_t s, const float* P, float* out, int64_t n, int Z) {
+  WD_LAUNCH(k_reduce_partials, grid1d(n), 256, 0, s, P, out, n, Z);
+  return WD_OK;
+}
+
+int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_t R, int N, int Z) {
+  int64_t rpc = ceil_div(R, Z);
+  WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc);
+  return reduce_partials(s, P, out, N, Z);
+}
+
+#define WD_TRY(expr) do { int _rc = (expr); if (_rc != WD_OK) return _rc; } while (0)
+
+// ---- forward ----------------------------------------------------------------------------------
+template <int ACT>
+int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, float* out,
+                 cudaStream_t s) {
+  const Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
+  const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim;
+  const int64_t Na = g.n_atoms, Nb = g.n_bonds, G = g.n_mols;
+  float* I = L.p(ws, L.I);
+  // input = W_i(f_bonds)                                                      mpn.py:96
+  AOperand a_in{g.f_bonds, nullptr, nullptr, nullptr, Fb, 0, 0};
+  { ProfScope ps(WD_PROF_INPUT_PROJ);
+  WD_TRY((gemm<A_PLAIN, B_NK, E_STORE, ACT, false>(c, s, a_in, w.W_i, Fb, c.bias ? w.b_i : nullptr, nullptr, 0,
+                                                  I, ld, Nb, h, Fb))); }
+  const float* prev = I;   // message = act(input) is applied on load (PREACT)          :97
+  for (int t = 1; t < c.depth; ++t) {                                               // :100
+    const bool pre = (t == 1);
+    float* A_t = L.p(ws, L.Agg) + (int64_t)(t - 1) * L.szA;
+    float* M_t = L.p(ws, L.M) + (int64_t)(t - 1) * L.szB;
+    const float* u = prev;
+    bool upre = pre;
+    if (c.undirected) {                                                             // :101-102
+      float* U = L.p(ws, L.U);
+      if (pre) WD_LAUNCH((k_symmetrize<ACT, true>), grid1d(Nb * nc4), 256, 0, s, prev, ld, g.rev, U, Nb, nc4);
+      else     WD_LAUNCH((k_symmetrize<ACT, false>), grid1d(Nb * nc4), 256, 0, s, prev, ld, g.rev, U, Nb, nc4);
+      u = U;
+      upre = false;
+    }
+    // a_message = sum_k w_bonds[a2b] * message[a2b]                                  :112-118
+    { ProfScope ps(WD_PROF_AGGREGATE);
+    if (upre) WD_LAUNCH((k_aggregate<ACT, true>), grid1d(Na * nc4), 256, 0, s, u, ld, g.w_bonds, g.in_ptr, g.in_idx, A_t, Na, nc4);
+    else      WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, u, ld, g.w_bonds, g.in_ptr, g.in_idx, A_t, Na, nc4); }
+    ProfScope ps(WD_PROF_DEPTH_STEP);
+    // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
+    AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
+    const float* bh = c.bias ? w.b_h : nullptr;
+    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h)));
+    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h)));
+    prev = M_t;
+  }
+  // final aggregate + atom update                                                    :127-134
+  float* A_d = L.p(ws, L.Agg) + (int64_t)(c.depth - 1) * L.szA;
+  { ProfScope ps(WD_PROF_AGGREGATE);
+  if (c.depth == 1) WD_LAUNCH((k_aggregate<ACT, true>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4);
+  else              WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4); }
+  float* H = L.p(ws, L.H);
+  AOperand a_o{g.f_atoms, A_d, nullptr, nullptr, Fa, ld, Fa};
+  { ProfScope ps(WD_PROF_ATOM_UPDATE);
+  WD_TRY((gemm<A_CONCAT, B_NK, E_ACT, ACT, false>(c, s, a_o, w.W_o, Fa + h, w.b_o, nullptr, 0, H, ld, Na, h, Fa + h))); }
+  // readout                                                                          :146-171
+  if (G > 0) {
+    ProfScope ps(WD_PROF_READOUT);
+    float* ms = L.p(ws, L.mscale);
+    WD_LAUNCH(k_mol_scale, grid1d(G), 256, 0, s, g.w_atoms, g.a_start, g.a_size, g.dop, c.aggregation,
+              c.aggregation_norm, ms, G);
+    WD_LAUNCH(k_readout, grid1d(G * h), 256, 0, s, H, ld, g.w_atoms, g.a_start, g.a_size, ms, out, h, G);
+  }
+  return WD_OK;
+}
+
+// ---- backward ---------------------------------------------------------------------------------
+template <int ACT, bool PREACT, bool HAS_DS, bool FIRST>
+int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const float* dA, const float* dS,
+                 const float* Y, int ld, float* dZ, float* dI) {
+  const int nc4 = ld / 4;
+  const int64_t Nb = g.n_bonds;
+  ProfScope ps(WD_PROF_MSG_GRAD);
+  if (c.undirected && HAS_DS)
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, FIRST>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
+              g.w_bonds, g.dst, g.rev, dZ, dI, Nb, nc4);
+  else
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, FIRST>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
+              g.w_bonds, g.dst, g.rev, dZ, dI, Nb, nc4);
+  return WD_OK;
+}
+
+template <int ACT>
+int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, const float* d_out,
+                  const WdGrads& gr, cudaStream_t s) {
+  const Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
+  const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim, Fo = Fa + h;
+  const int64_t Na = g.n_atoms, Nb = g.n_bonds;
+  const int d = c.depth;
+  float *I = L.p(ws, L.I), *H = L.p(ws, L.H), *dZ = L.p(ws, L.dZ), *dS = L.p(ws, L.dS), *dI = L.p(ws, L.dI),
+        *dA = L.p(ws, L.dA), *dZo = L.p(ws, L.dZo), *P = L.p(ws, L.partials);
+  const int64_t pw = std::max<int64_t>((int64_t)std::max(1, d - 1) * h * h, (int64_t)h * std::max(Fo, Fb));
+  float* Pcol = P + (int64_t)L.Z * pw;   // column-sum partials
+  float* A_d = L.p(ws, L.Agg) + (int64_t)(d - 1) * L.szA;
+
+  // readout + atom-update activation:  dZo = w_a * dop/den * d_out[mol] * act'(H)
+  { ProfScope ps(WD_PROF_READOUT);
+  WD_LAUNCH((k_readout_grad<ACT>), grid1d(Na * ld), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
+            L.p(ws, L.mscale), dZo, Na); }
+  {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
+    ProfScope ps(WD_PROF_DW);
+    const int Z = dw_chunks(Na, h, Fo);
+    AOperand y{g.f_atoms, A_d, nullptr, nullptr, Fa, ld, Fa};
+    WD_TRY((dw_partial<A_CONCAT, ACT, false>(s, dZo, ld, y, P, Na, h, Fo, Z)));
+    WD_TRY(reduce_partials(s, P, gr.dW_o, (int64_t)h * Fo, Z));
+    WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, Z));
+  }
+  // dA_d = dZo * W_o[:, F_a:]
+  AOperand a_zo{dZo, nullptr, nullptr, nullptr, ld, 0, 0};
+  { ProfScope ps(WD_PROF_DX);
+  WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_zo, w.W_o + Fa, Fo, nullptr, nullptr, 0, dA, ld, Na, h, h))); }
+
+  const int Zh = dw_chunks(Nb, h, h);
+  for (int t = d - 1; t >= 1; --t) {
+    const float* M_t = L.p(ws, L.M) + (int64_t)(t - 1) * L.szB;
+    const float* A_t = L.p(ws, L.Agg) + (int64_t)(t - 1) * L.szA;
+    const float* M_prev = (t == 1) ? I : L.p(ws, L.M) + (int64_t)(t - 2) * L.szB;
+    const bool pre = (t == 1);
+    // dZ_t = dM_t * act'(M_t), dI += dZ_t ; dM_t = w_b dA[dst b] - dS[rev b] (symmetrised if undirected)
+    if (t == d - 1) WD_TRY((message_grad<ACT, false, false, true>(c, s, g, dA, dS, M_t, ld, dZ, dI)));
+    else            WD_TRY((message_grad<ACT, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, dI)));
+    // dW_h += dZ_t^T S_t, with S_t = A_t[b2a] - U_{t-1}[b2revb] recomputed, never stored
+    const float* u = M_prev;
+    bool upre = pre;
+    if (c.undirected) {
+      float* U = L.p(ws, L.U);
+      if (pre) WD_LAUNCH((k_symmetrize<ACT, true>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
+      else     WD_LAUNCH((k_symmetrize<ACT, false>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
+      u = U;
+      upre = false;
+    }
+    AOperand y{A_t, u, g.src, g.rev, ld, ld, 0};
+    float* Pt = P + (int64_t)(d - 1 - t) * Zh * h * h;
+    { ProfScope ps(WD_PROF_DW);
+    if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(s, dZ, ld, y, Pt, Nb, h, h, Zh)));
+    else      WD_TRY((dw_partial<A_GATHER_DIFF, ACT, false>(s, dZ, ld, y, Pt, Nb, h, h, Zh))); }
+    // dS = dZ_t * W_h ; dA[a] = sum over out-edges of a of dS  (transpose-CSR, no atomics)
+    AOperand a_z{dZ, nullptr, nullptr, nullptr, ld, 0, 0};
+    { ProfScope ps(WD_PROF_DX);
+    WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_z, w.W_h, h, nullptr, nullptr, 0, dS, ld, Nb, h, h))); }
+    ProfScope ps(WD_PROF_SCATTER);
+    WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, dS, ld, nullptr, g.in_ptr, g.out_idx, dA, Na, nc4);
+  }
+  if (d > 1) {
+    { ProfScope ps(WD_PROF_DW);
+    WD_TRY(reduce_partials(s, P, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
+    if (c.bias && gr.db_h) WD_TRY(colsum(s, dI, ld, Pcol, gr.db_h, Nb, h, Zh)); }  // dI == sum_{t>=1} dZ_t here
+    WD_TRY((message_grad<ACT, true, true, false>(c, s, g, dA, dS, I, ld, dZ, dI)));
+  } else {
+    WD_CUDA_OK(cudaMemsetAsync(gr.dW_h, 0, sizeof(float) * h * h, s));
+    if (c.bias && gr.db_h) WD_CUDA_OK(cudaMemsetAsync(gr.db_h, 0, sizeof(float) * h, s));
+    WD_TRY((message_grad<ACT, true, false, true>(c, s, g, dA, dS, I, ld, dZ, dI)));
+  }
+  {  // dW_i = dI^T f_bonds ; db_i = colsum(dI)
+    ProfScope ps(WD_PROF_DW);
+    const int Z = dw_chunks(Nb, h, Fb);
+    AOperand y{g.f_bonds, nullptr, nullptr, nullptr, Fb, 0, 0};
+    WD_TRY((dw_partial<A_PLAIN, ACT, false>(s, dI, ld, y, P, Nb, h, Fb, Z)));
+    WD_TRY(reduce_partials(s, P, gr.dW_i, (int64_t)h * Fb, Z));
+    if (c.bias && gr.db_i) WD_TRY(colsum(s, dI, ld, Pcol, gr.db_i, Nb, h, Z));
+  }
+  return WD_OK;
+}
+
+}  // namespace
+}  // namespace wd
+
+// ---- C ABI --------------------------------------------------------------------------------------
+extern "C" size_t wd_workspace_bytes(const WdConfig* cfg, int64_t n_atoms, int64_t n_bonds, int64_t n_mols) {
+  if (wd::check_cfg(cfg) != WD_OK || n_atoms < 1 || n_bonds < 1 || n_mols < 0) return 0;
+  return (size_t)wd::make_layout(*cfg, n_atoms, n_bonds, n_mols).total * sizeof(float);
+}
+
+extern "C" int wd_encoder_forward(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,
+                                  void* workspace, size_t workspace_bytes, float* out, void* stream) {
+  using namespace wd;
+  WD_TRY(check_cfg(cfg));
+  WD_TRY(check_graph(graph, weights, cfg));
+  if (!workspace || (graph->n_mols > 0 && !out)) return fail(WD_ERR_INVALID_ARG, "workspace/out is NULL");
+  if (workspace_bytes < wd_workspace_bytes(cfg, graph->n_atoms, graph->n_bonds, graph->n_mols))
+    return fail(WD_ERR_INVALID_ARG, "workspace too small: %zu < %zu bytes", workspace_bytes,
+                wd_workspace_bytes(cfg, graph->n_atoms, graph->n_bonds, graph->n_mols));
+  if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
+    return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
+  int rc = WD_OK;
+  WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream));
+  return rc;
+}
+
+extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,
+                                   void* workspace, size_t workspace_bytes, const float* d_out,
+                                   const WdGrads* grads, void* stream) {
+  using namespace wd;
+  WD_TRY(check_cfg(cfg));
+  WD_TRY(check_graph(graph, weights, cfg));
+  if (!workspace || !grads || !grads->dW_i || !grads->dW_h || !grads->dW_o || !grads->db_o ||
+      (graph->n_mols > 0 && !d_out))
+    return fail(WD_ERR_INVALID_ARG, "workspace/grads/d_out is NULL");
+  if (workspace_bytes < wd_workspace_bytes(cfg, graph->n_atoms, graph->n_bonds, graph->n_mols))
+    return fail(WD_ERR_INVALID_ARG, "workspace too small");
+  int rc = WD_OK;
+  WD_DISPATCH_ACT(cfg->activation,
+                  rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, (cudaStream_t)stream));
+  return rc;
+}
+
+extern "C" const char* wd_last_error(void) { return wd::g_err; }
+extern "C" int64_t wd_launch_count(void) { return wd::g_launches.load(); }
+extern "C" int wd_abi_version(void) { return 1; }

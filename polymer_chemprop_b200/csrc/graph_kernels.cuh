@@ -1,0 +1,141 @@
+// HBM-bound graph kernels of the encoder: CSR aggregate / transpose-CSR scatter, the backward
+// message-gradient kernel, undirected symmetrisation and the weighted per-molecule readout.
+// All use one thread per (row, float4 column): adjacent lanes read adjacent 16-byte words of the
+// same row, so every gathered row is fetched as full 128-byte lines.  No atomics anywhere.
+#pragma once
+#include "common.cuh"
+
+namespace wd {
+
+// out[a, :] = sum_{j in [ptr[a], ptr[a+1])} w[idx[j]] * U(idx[j], :)
+//   forward : idx = in_idx,  w = w_bonds   (a_message, mpn.py:112-118 / :127-131)
+//   backward: idx = out_idx, w = nullptr   (dA[a] = sum over out-edges of dS, transpose of a_message[b2a])
+template <int ACT, bool PREACT>
+__global__ void k_aggregate(const float* __restrict__ U, int ld, const float* __restrict__ w,
+                            const int32_t* __restrict__ ptr, const int32_t* __restrict__ idx,
+                            float* __restrict__ out, int64_t n_rows, int nc4) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows * nc4) return;
+  int64_t a = i / nc4;
+  int c = (int)(i - a * nc4) * 4;
+  int j0 = __ldg(ptr + a), j1 = __ldg(ptr + a + 1);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = j0; j < j1; ++j) {
+    int b = __ldg(idx + j);
+    float4 v = ldg4(U + (int64_t)b * ld + c);
+    if (PREACT) v = f4_act<ACT>(v);
+    acc = f4_fma(w ? __ldg(w + b) : 1.f, v, acc);
+  }
+  st4(out + a * ld + c, acc);
+}
+
+// U[b] = (X(b) + X(rev b)) / 2      (mpn.py:101-102)
+template <int ACT, bool PREACT>
+__global__ void k_symmetrize(const float* __restrict__ X, int ld, const int32_t* __restrict__ rev,
+                             float* __restrict__ U, int64_t n_rows, int nc4) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows * nc4) return;
+  int64_t b = i / nc4;
+  int c = (int)(i - b * nc4) * 4;
+  float4 x = ldg4(X + b * ld + c), y = ldg4(X + (int64_t)__ldg(rev + b) * ld + c);
+  if (PREACT) { x = f4_act<ACT>(x); y = f4_act<ACT>(y); }
+  st4(U + b * ld + c, make_float4((x.x + y.x) / 2.f, (x.y + y.y) / 2.f, (x.z + y.z) / 2.f, (x.w + y.w) / 2.f));
+}
+
+// Backward of one message-passing step's inputs:
+//   g(b)  = w_b * dA[dst b] - dS[rev b]              (dS absent for the last step: HAS_DS = false)
+//   UNDIRECTED && HAS_DS:  g(b) = (g(b) + g(rev b)) / 2
+//   dZ[b] = g(b) * act'(Y[b])   with Y = M_t (PREACT: Y = act(I))
+//   dI[b] = (FIRST ? 0 : dI[b]) + dZ[b]
+template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool FIRST>
+__global__ void k_message_grad(const float* __restrict__ dA, const float* __restrict__ dS,
+                               const float* __restrict__ Y, int ld, const float* __restrict__ w,
+                               const int32_t* __restrict__ dst, const int32_t* __restrict__ rev,
+                               float* __restrict__ dZ, float* __restrict__ dI, int64_t n_rows, int nc4) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows * nc4) return;
+  int64_t b = i / nc4;
+  int c = (int)(i - b * nc4) * 4;
+  float wb = __ldg(w + b);
+  float4 da = ldg4(dA + (int64_t)__ldg(dst + b) * ld + c);
+  float4 g = make_float4(wb * da.x, wb * da.y, wb * da.z, wb * da.w);
+  if (HAS_DS) {
+    int r = __ldg(rev + b);
+    float4 ds = ldg4(dS + (int64_t)r * ld + c);
+    g.x -= ds.x; g.y -= ds.y; g.z -= ds.z; g.w -= ds.w;
+    if (UNDIRECTED) {
+      float wr = __ldg(w + r);
+      float4 dar = ldg4(dA + (int64_t)__ldg(dst + r) * ld + c);
+      float4 dsb = ldg4(dS + b * ld + c);
+      g.x = (g.x + (wr * dar.x - dsb.x)) / 2.f; g.y = (g.y + (wr * dar.y - dsb.y)) / 2.f;
+      g.z = (g.z + (wr * dar.z - dsb.z)) / 2.f; g.w = (g.w + (wr * dar.w - dsb.w)) / 2.f;
+    }
+  }
+  float4 y = ldg4(Y + b * ld + c);
+  if (PREACT) y = f4_act<ACT>(y);
+  float4 dz = make_float4(g.x * act_bwd_from_out<ACT>(y.x), g.y * act_bwd_from_out<ACT>(y.y),
+                          g.z * act_bwd_from_out<ACT>(y.z), g.w * act_bwd_from_out<ACT>(y.w));
+  st4(dZ + b * ld + c, dz);
+  if (FIRST) {
+    st4(dI + b * ld + c, dz);
+  } else {
+    float4 di = *reinterpret_cast<const float4*>(dI + b * ld + c);
+    st4(dI + b * ld + c, make_float4(di.x + dz.x, di.y + dz.y, di.z + dz.z, di.w + dz.w));
+  }
+}
+
+// mscale[g] = dop[g] / den[g], den = sum w_atoms | 1 | aggregation_norm  (mpn.py:158-167);
+// 0 for empty molecules (cached_zero_vector branch, :148-149).
+__global__ void k_mol_scale(const float* __restrict__ w_atoms, const int32_t* __restrict__ a_start,
+                            const int32_t* __restrict__ a_size, const float* __restrict__ dop,
+                            int aggregation, float aggregation_norm, float* __restrict__ mscale,
+                            int64_t n_mols) {
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_mols) return;
+  int s = a_start[g], n = a_size[g];
+  if (n == 0) { mscale[g] = 0.f; return; }
+  float den = 1.f;
+  if (aggregation == WD_AGG_MEAN) {
+    den = 0.f;
+    for (int i = 0; i < n; ++i) den += w_atoms[s + i];
+  } else if (aggregation == WD_AGG_NORM) {
+    den = aggregation_norm;
+  }
+  mscale[g] = dop[g] / den;
+}
+
+// out[g, :] = mscale[g] * sum_{a in scope g} w_atoms[a] * H[a, :]      (mpn.py:146-171)
+__global__ void k_readout(const float* __restrict__ H, int ld, const float* __restrict__ w_atoms,
+                          const int32_t* __restrict__ a_start, const int32_t* __restrict__ a_size,
+                          const float* __restrict__ mscale, float* __restrict__ out, int h,
+                          int64_t n_mols) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_mols * h) return;
+  int64_t g = i / h;
+  int c = (int)(i - g * h);
+  int s = a_start[g], n = a_size[g];
+  float acc = 0.f;
+  for (int k = 0; k < n; ++k) acc = fmaf(__ldg(w_atoms + s + k), __ldg(H + (int64_t)(s + k) * ld + c), acc);
+  out[g * h + c] = mscale[g] * acc;
+}
+
+// dZo[a, :] = w_atoms[a] * mscale[mol a] * d_out[mol a, :] * act'(H[a, :])   (0 for atoms in no scope)
+template <int ACT>
+__global__ void k_readout_grad(const float* __restrict__ d_out, int h, const float* __restrict__ H,
+                               int ld, const float* __restrict__ w_atoms,
+                               const int32_t* __restrict__ mol_of, const float* __restrict__ mscale,
+                               float* __restrict__ dZo, int64_t n_atoms) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_atoms * ld) return;
+  int64_t a = i / ld;
+  int c = (int)(i - a * ld);
+  int g = __ldg(mol_of + a);
+  float v = 0.f;
+  if (g >= 0 && c < h) {
+    float s = __ldg(w_atoms + a) * __ldg(mscale + g);
+    v = s * __ldg(d_out + (int64_t)g * h + c) * act_bwd_from_out<ACT>(H[a * ld + c]);
+  }
+  dZo[a * ld + c] = v;
+}
+
+}  // namespace wd

@@ -1,0 +1,195 @@
+// fp32 CUDA-core contraction kernels (math_mode FP32: the <=1e-5 parity path).
+// Register-blocked smem-tiled FFMA; A operands are virtual (operands.cuh), epilogues fused.
+#pragma once
+#include "operands.cuh"
+
+namespace wd {
+
+// ---------------------------------------------------------------------------------------------
+// C[M, ldc] (first N columns, the rest zero-filled) = epi( A[M,K] * B[N,K]^T )
+// tile 128 x 64 x 16, 256 threads, 8 x 4 outputs per thread.
+// ---------------------------------------------------------------------------------------------
+constexpr int SG_BM = 128, SG_BN = 64, SG_BK = 16, SG_THREADS = 256;
+
+template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
+__global__ void __launch_bounds__(SG_THREADS)
+k_simt_gemm(AOperand A, const float* __restrict__ W, int ldb, const float* __restrict__ bias,
+            const float* __restrict__ R, int ldr, float* __restrict__ C, int ldc, int64_t M, int N,
+            int K) {
+  __shared__ float As[SG_BK][SG_BM + 4];
+  __shared__ float Bs[SG_BK][SG_BN + 4];
+  const int tid = threadIdx.x;
+  const int64_t row0 = (int64_t)blockIdx.x * SG_BM;
+  const int col0 = blockIdx.y * SG_BN;
+  const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 thread grid: 8 rows x 4 cols each
+
+  // A-load mapping: thread loads rows (tid>>4) + 16*i, column k = tid & 15
+  const int lk = tid & 15;
+  int sr[8], rr[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int64_t r = row0 + (tid >> 4) + 16 * i;
+    sr[i] = rr[i] = 0;
+    if (AMODE == A_GATHER_DIFF && r < M) {
+      sr[i] = __ldg(A.src + r);
+      rr[i] = __ldg(A.rev + r);
+    }
+  }
+  float acc[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += SG_BK) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int rl = (tid >> 4) + 16 * i;
+      int64_t r = row0 + rl;
+      int k = k0 + lk;
+      float v = 0.f;
+      if (r < M && k < K) v = a_elem<AMODE, ACT, PREACT>(A, r, k, sr[i], rr[i]);
+      As[lk][rl] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float v = 0.f;
+      if (BMODE == B_NK) {  // k fastest in memory
+        int nl = (tid >> 4) + 16 * i, n = col0 + nl, k = k0 + lk;
+        if (n < N && k < K) v = __ldg(W + (int64_t)n * ldb + k);
+        Bs[lk][nl] = v;
+      } else {              // n fastest in memory
+        int nl = tid & 63, kl = (tid >> 6) + 4 * i, n = col0 + nl, k = k0 + kl;
+        if (n < N && k < K) v = __ldg(W + (int64_t)k * ldb + n);
+        Bs[kl][nl] = v;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < SG_BK; ++kk) {
+      float a[8], b[4];
+      float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
+      float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
+      float4 b0 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
+      a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+      b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  const int n0 = col0 + tx * 4;
+  if (n0 >= ldc) return;
+  float bv[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) bv[j] = (bias != nullptr && n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int64_t r = row0 + ty * 8 + i;
+    if (r >= M) continue;
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float v = acc[i][j] + bv[j];
+      if (EPI == E_RES_ACT) v += (n0 + j < N) ? __ldg(R + r * ldr + n0 + j) : 0.f;
+      if (EPI != E_STORE) v = act_fwd<ACT>(v);
+      o[j] = (n0 + j < N) ? v : 0.f;   // pad columns [N, ldc) are kept at zero
+    }
+    st4(C + r * ldc + n0, make_float4(o[0], o[1], o[2], o[3]));  // ldc % 4 == 0, n0 % 4 == 0
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Weight-gradient contraction over the row (bond / atom) dimension, deterministic split:
+//   P[z][n1, n2] = sum_{r in chunk z} X[r, n1] * Y(r, n2)        (Y virtual, operands.cuh)
+// followed by k_reduce_partials (fixed z order).  tile 64 x 64, 16 rows per step.
+// ---------------------------------------------------------------------------------------------
+constexpr int DW_BM = 64, DW_BN = 64, DW_BK = 16, DW_THREADS = 256;
+
+template <int YMODE, int ACT, bool PREACT>
+__global__ void __launch_bounds__(DW_THREADS)
+k_simt_dw(const float* __restrict__ X, int ldx, AOperand Y, float* __restrict__ P, int64_t R,
+          int N1, int N2, int64_t rows_per_chunk) {
+  __shared__ float Xs[DW_BK][DW_BM + 4];
+  __shared__ float Ys[DW_BK][DW_BN + 4];
+  const int tid = threadIdx.x;
+  const int n1_0 = blockIdx.y * DW_BM, n2_0 = blockIdx.x * DW_BN;
+  const int64_t r_begin = (int64_t)blockIdx.z * rows_per_chunk;
+  const int64_t r_end = min(R, r_begin + rows_per_chunk);
+  const int ty = tid >> 4, tx = tid & 15;  // 4 x 4 outputs per thread
+  const int lc = tid & 63, lr = tid >> 6;  // load: column lc, rows lr + 4*i
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int64_t r0 = r_begin; r0 < r_end; r0 += DW_BK) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int rl = lr + 4 * i;
+      int64_t r = r0 + rl;
+      float xv = 0.f, yv = 0.f;
+      if (r < r_end) {
+        if (n1_0 + lc < N1) xv = __ldg(X + r * ldx + n1_0 + lc);
+        if (n2_0 + lc < N2) {
+          int s = 0, rv = 0;
+          if (YMODE == A_GATHER_DIFF) { s = __ldg(Y.src + r); rv = __ldg(Y.rev + r); }
+          yv = a_elem<YMODE, ACT, PREACT>(Y, r, n2_0 + lc, s, rv);
+        }
+      }
+      Xs[rl][lc] = xv;
+      Ys[rl][lc] = yv;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < DW_BK; ++kk) {
+      float4 a = *reinterpret_cast<const float4*>(&Xs[kk][ty * 4]);
+      float4 b = *reinterpret_cast<const float4*>(&Ys[kk][tx * 4]);
+      float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* Pz = P + (int64_t)blockIdx.z * N1 * N2;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int n1 = n1_0 + ty * 4 + i;
+    if (n1 >= N1) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int n2 = n2_0 + tx * 4 + j;
+      if (n2 < N2) Pz[(int64_t)n1 * N2 + n2] = acc[i][j];
+    }
+  }
+}
+
+// column sums over a row chunk: P[z][n] = sum_{r in chunk z} X[r, n]   (bias gradients)
+__global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __restrict__ P,
+                                 int64_t R, int N, int64_t rows_per_chunk) {
+  int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  int64_t r_begin = (int64_t)blockIdx.y * rows_per_chunk, r_end = min(R, r_begin + rows_per_chunk);
+  float s = 0.f;
+  for (int64_t r = r_begin; r < r_end; ++r) s += __ldg(X + r * ldx + n);
+  P[(int64_t)blockIdx.y * N + n] = s;
+}
+
+// out[i] = sum_z P[z][i] in ascending z (fixed order => bitwise reproducible)
+__global__ void k_reduce_partials(const float* __restrict__ P, float* __restrict__ out, int64_t n,
+                                  int Z) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.f;
+  for (int z = 0; z < Z; ++z) s += P[(int64_t)z * n + i];
+  out[i] = s;
+}
+
+}  // namespace wd

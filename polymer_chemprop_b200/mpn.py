@@ -1,0 +1,276 @@
+"""Drop-in ``MPN`` / ``MPNEncoder`` (chemprop/models/mpn.py:14-289) backed by libwdmpnn.so.
+
+Same constructor arguments, attribute names, sub-module / parameter names
+(``encoder.<i>.W_i|W_h|W_o``, ``cached_zero_vector``) and ``forward`` signatures as the
+reference, so ``MoleculeModel`` (chemprop/models/model.py:41-47) and existing checkpoints
+(chemprop/utils.py:98-135, :194) work unchanged.  The arithmetic runs in hand-written sm_100a
+kernels through the C ABI; there is no CPU / eager fallback.
+"""
+import ctypes as C
+from functools import reduce
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _capi
+from .graph import ATOM_FDIM, BOND_ONLY_FDIM, BatchMolGraph
+
+
+def get_activation_function(activation: str) -> nn.Module:
+    """chemprop/nn_utils.py:70-99."""
+    table = {"ReLU": nn.ReLU, "LeakyReLU": lambda: nn.LeakyReLU(0.1), "PReLU": nn.PReLU,
+             "tanh": nn.Tanh, "SELU": nn.SELU, "ELU": nn.ELU}
+    if activation not in table:
+        raise ValueError(f'Activation "{activation}" not supported.')
+    return table[activation]()
+
+
+class DeviceGraph:
+    """Device-resident form of one BatchMolGraph: the get_components() tensors moved once, plus the
+    int32 CSR / reverse-CSR arrays rebuilt on the device by wd_csr_build.  Cached on the
+    BatchMolGraph instance (like the reference caches a2a / b2b, featurization.py:812-813)."""
+
+    def __init__(self, mol_graph, device: torch.device, validate: bool = True):
+        f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, a_scope, _b_scope, dop = \
+            mol_graph.get_components(atom_messages=False)
+        f32 = dict(device=device, dtype=torch.float32)
+        i64 = dict(device=device, dtype=torch.int64)
+        self.device = device
+        self.f_atoms = f_atoms.to(**f32).contiguous()          # mpn.py:84-87
+        self.f_bonds = f_bonds.to(**f32).contiguous()
+        self.w_atoms = w_atoms.to(**f32).contiguous()
+        self.w_bonds = w_bonds.to(**f32).contiguous()
+        a2b = a2b.to(**i64).contiguous()
+        b2a = b2a.to(**i64).contiguous()
+        b2revb = b2revb.to(**i64).contiguous()
+        self.n_atoms, self.n_bonds, self.n_mols = self.f_atoms.shape[0], self.f_bonds.shape[0], len(a_scope)
+        self.atom_fdim, self.bond_fdim = self.f_atoms.shape[1], self.f_bonds.shape[1]
+        if a2b.dim() != 2 or a2b.shape[0] != self.n_atoms:
+            raise ValueError("a2b must be [n_atoms, max_num_bonds]")
+        scope = np.asarray(a_scope, dtype=np.int64).reshape(-1, 2)
+        host = torch.from_numpy(np.concatenate([scope[:, 0], scope[:, 1]]).astype(np.int32))
+        dop_h = torch.tensor([float(x) for x in dop], dtype=torch.float32)
+        if device.type == "cuda":
+            host, dop_h = host.pin_memory(), dop_h.pin_memory()
+        scopes = host.to(device, non_blocking=True)
+        self.a_start, self.a_size = scopes[:self.n_mols], scopes[self.n_mols:]
+        self.dop = dop_h.to(device, non_blocking=True)
+        i32 = dict(device=device, dtype=torch.int32)
+        self.in_ptr = torch.empty(self.n_atoms + 1, **i32)
+        self.in_idx = torch.empty(max(self.n_bonds - 1, 1), **i32)
+        self.out_idx = torch.empty(max(self.n_bonds - 1, 1), **i32)
+        self.src = torch.empty(self.n_bonds, **i32)
+        self.rev = torch.empty(self.n_bonds, **i32)
+        self.dst = torch.empty(self.n_bonds, **i32)
+        self.mol_of = torch.empty(self.n_atoms, **i32)
+        self.flags = torch.empty(4, **i32)
+        L, p = _capi.lib(), _capi.ptr
+        stream = _capi.current_stream(device)
+        _capi.check(L.wd_csr_build(p(a2b), self.n_atoms, a2b.shape[1], p(b2a), p(b2revb), self.n_bonds,
+                                   p(self.a_start), p(self.a_size), self.n_mols, p(self.in_ptr),
+                                   p(self.in_idx), p(self.out_idx), p(self.src), p(self.rev), p(self.dst),
+                                   p(self.mol_of), p(self.flags), stream))
+        if validate:
+            _capi.check(L.wd_csr_build_check(p(self.flags), stream))
+        self.struct = _capi.WdGraph(
+            self.n_atoms, self.n_bonds, self.n_mols, p(self.f_atoms), p(self.f_bonds), p(self.w_atoms),
+            p(self.w_bonds), p(self.in_ptr), p(self.in_idx), p(self.out_idx), p(self.src), p(self.rev),
+            p(self.dst), p(self.mol_of), p(self.a_start), p(self.a_size), p(self.dop))
+
+    @staticmethod
+    def get(mol_graph, device: torch.device) -> "DeviceGraph":
+        cache = getattr(mol_graph, "_wd_cache", None)
+        if cache is None:
+            cache = {}
+            try:
+                mol_graph._wd_cache = cache
+            except AttributeError:
+                pass
+        key = (device.type, device.index)
+        if key not in cache:
+            cache[key] = DeviceGraph(mol_graph, device)
+        return cache[key]
+
+
+class _EncoderFunction(torch.autograd.Function):
+    """forward = wd_encoder_forward, backward = wd_encoder_backward (deterministic)."""
+
+    @staticmethod
+    def forward(ctx, enc, dg, W_i, b_i, W_h, b_h, W_o, b_o):
+        dev = dg.device
+        cfg = enc._config(dg)
+        ws_bytes = _capi.lib().wd_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
+        if ws_bytes == 0:
+            _capi.check(_capi.WD_ERR_INVALID_ARG)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        out = torch.empty((dg.n_mols, enc.hidden_size), dtype=torch.float32, device=dev)
+        ws_c = [t.detach().contiguous() if t is not None else None for t in (W_i, b_i, W_h, b_h, W_o, b_o)]
+        weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
+        _capi.check(_capi.lib().wd_encoder_forward(C.byref(dg.struct), C.byref(weights), C.byref(cfg),
+                                                   _capi.ptr(ws), ws_bytes, _capi.ptr(out),
+                                                   _capi.current_stream(dev)))
+        ctx.enc, ctx.dg, ctx.cfg, ctx.ws, ctx.ws_bytes, ctx.weights_c = enc, dg, cfg, ws, ws_bytes, ws_c
+        ctx.has_bias = b_i is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, d_out):
+        enc, dg, cfg = ctx.enc, ctx.dg, ctx.cfg
+        dev = dg.device
+        W_i, b_i, W_h, b_h, W_o, b_o = ctx.weights_c
+        d_out = d_out.contiguous().float()
+        gW_i, gW_h, gW_o, gb_o = (torch.empty_like(t) for t in (W_i, W_h, W_o, b_o))
+        gb_i = torch.empty_like(b_i) if ctx.has_bias else None
+        gb_h = torch.empty_like(b_h) if ctx.has_bias else None
+        weights = _capi.WdWeights(*[_capi.ptr(t) for t in ctx.weights_c])
+        grads = _capi.WdGrads(*[_capi.ptr(t) for t in (gW_i, gb_i, gW_h, gb_h, gW_o, gb_o)])
+        _capi.check(_capi.lib().wd_encoder_backward(C.byref(dg.struct), C.byref(weights), C.byref(cfg),
+                                                    _capi.ptr(ctx.ws), ctx.ws_bytes, _capi.ptr(d_out),
+                                                    C.byref(grads), _capi.current_stream(dev)))
+        ctx.ws = None
+        if enc.depth == 1:          # W_h is unused by the reference's graph when depth == 1
+            gW_h, gb_h = None, None
+        return None, None, gW_i, gb_i, gW_h, gb_h, gW_o, gb_o
+
+
+class MPNEncoder(nn.Module):
+    """Drop-in for chemprop.models.mpn.MPNEncoder (mpn.py:14-173)."""
+
+    def __init__(self, args, atom_fdim: int, bond_fdim: int):
+        super().__init__()
+        self.atom_fdim = atom_fdim
+        self.bond_fdim = bond_fdim
+        self.atom_messages = args.atom_messages
+        self.hidden_size = args.hidden_size
+        self.bias = args.bias
+        self.depth = args.depth
+        self.dropout = args.dropout
+        self.layers_per_message = 1
+        self.undirected = args.undirected
+        self.device = args.device
+        self.aggregation = args.aggregation
+        self.aggregation_norm = args.aggregation_norm
+        self.math_mode = getattr(args, "wd_math_mode", None) or _default_math_mode()
+        if self.atom_messages:
+            raise NotImplementedError("atom_messages=True is not accelerated by the B200 encoder; "
+                                      "use chemprop.models.mpn.MPNEncoder for that mode")
+        if getattr(args, "atom_descriptors", None) == "descriptor":
+            raise NotImplementedError("atom_descriptors='descriptor' is not accelerated by the B200 encoder; "
+                                      "use chemprop.models.mpn.MPNEncoder for that mode")
+        if args.activation not in _capi.ACTIVATIONS:
+            raise NotImplementedError(f'activation "{args.activation}" is not supported by the B200 encoder '
+                                      f"(supported: {sorted(_capi.ACTIVATIONS)})")
+        if self.aggregation not in _capi.AGGREGATIONS:
+            raise ValueError(f'aggregation "{self.aggregation}" not supported')
+        if self.math_mode not in _capi.MATH_MODES:
+            raise ValueError(f'wd_math_mode "{self.math_mode}" not in {sorted(_capi.MATH_MODES)}')
+        self.activation = args.activation
+        self.dropout_layer = nn.Dropout(p=self.dropout)
+        self.act_func = get_activation_function(args.activation)
+        self.cached_zero_vector = nn.Parameter(torch.zeros(self.hidden_size), requires_grad=False)
+        self.W_i = nn.Linear(self.bond_fdim, self.hidden_size, bias=self.bias)
+        self.W_h = nn.Linear(self.hidden_size, self.hidden_size, bias=self.bias)
+        self.W_o = nn.Linear(self.atom_fdim + self.hidden_size, self.hidden_size)
+
+    def _config(self, dg: DeviceGraph) -> _capi.WdConfig:
+        return _capi.WdConfig(self.hidden_size, dg.atom_fdim, dg.bond_fdim, self.depth,
+                              _capi.ACTIVATIONS[self.activation], _capi.AGGREGATIONS[self.aggregation],
+                              int(bool(self.undirected)), int(bool(self.bias)),
+                              _capi.MATH_MODES[self.math_mode], float(self.aggregation_norm))
+
+    def forward(self, mol_graph, atom_descriptors_batch: List[np.ndarray] = None) -> torch.Tensor:
+        """Encodes a batch of molecular graphs -> [num_molecules, hidden_size] (mpn.py:66-173)."""
+        if atom_descriptors_batch is not None:
+            raise NotImplementedError("atom descriptors are not accelerated by the B200 encoder")
+        if self.training and self.dropout > 0.0:
+            raise NotImplementedError("dropout > 0 in training mode is not implemented in the B200 encoder "
+                                      "(the reference's RNG stream cannot be matched); use dropout=0")
+        device = self.W_i.weight.device
+        if device.type != "cuda":
+            raise RuntimeError("the B200 encoder runs on CUDA devices only (no CPU fallback); "
+                               f"parameters are on {device}")
+        dg = DeviceGraph.get(mol_graph, device)
+        if dg.atom_fdim != self.atom_fdim or dg.bond_fdim != self.bond_fdim:
+            raise ValueError(f"feature dims of the batch ({dg.atom_fdim}, {dg.bond_fdim}) do not match the "
+                             f"encoder ({self.atom_fdim}, {self.bond_fdim})")
+        return _EncoderFunction.apply(self, dg, self.W_i.weight, self.W_i.bias, self.W_h.weight,
+                                      self.W_h.bias, self.W_o.weight, self.W_o.bias)
+
+
+def _default_math_mode() -> str:
+    import os
+    return os.environ.get("WDMPNN_MATH", "fp32")
+
+
+class MPN(nn.Module):
+    """Drop-in for chemprop.models.mpn.MPN (mpn.py:176-289)."""
+
+    def __init__(self, args, atom_fdim: int = None, bond_fdim: int = None):
+        super().__init__()
+        if (atom_fdim is None or bond_fdim is None) and (args.overwrite_default_atom_features or
+                                                         args.overwrite_default_bond_features):
+            raise NotImplementedError("overwrite_default_*_features needs explicit atom_fdim / bond_fdim "
+                                      "(the reference resolves them from featurisation globals)")
+        self.atom_fdim = atom_fdim or ATOM_FDIM                      # get_atom_fdim(), featurization.py
+        self.bond_fdim = bond_fdim or (self.atom_fdim + BOND_ONLY_FDIM)
+        self.features_only = args.features_only
+        self.use_input_features = args.use_input_features
+        self.device = args.device
+        self.atom_descriptors = args.atom_descriptors
+        self.overwrite_default_atom_features = args.overwrite_default_atom_features
+        self.overwrite_default_bond_features = args.overwrite_default_bond_features
+        if self.features_only:
+            return
+        if args.mpn_shared:                                         # mpn.py:204-208
+            self.encoder = nn.ModuleList([MPNEncoder(args, self.atom_fdim, self.bond_fdim)] *
+                                         args.number_of_molecules)
+        else:
+            self.encoder = nn.ModuleList([MPNEncoder(args, self.atom_fdim, self.bond_fdim)
+                                          for _ in range(args.number_of_molecules)])
+
+    def forward(self, batch, features_batch: List[np.ndarray] = None,
+                atom_descriptors_batch: List[np.ndarray] = None,
+                atom_features_batch: List[np.ndarray] = None,
+                bond_features_batch: List[np.ndarray] = None) -> torch.Tensor:
+        if not hasattr(batch[0], "get_components"):                 # mpn.py:229-264 (SMILES / RDKit mols)
+            try:
+                from chemprop.features import mol2graph             # needs the reference + RDKit
+            except Exception as e:
+                raise NotImplementedError("featurising SMILES / RDKit molecules needs chemprop.features."
+                                          "mol2graph (RDKit); pass BatchMolGraph objects instead") from e
+            batch = [[mols[i] for mols in batch] for i in range(len(batch[0]))]
+            if self.atom_descriptors == "feature" or bond_features_batch is not None:
+                if len(batch) > 1:
+                    raise NotImplementedError("Atom/bond descriptors are currently only supported with one "
+                                              "molecule per input (i.e., number_of_molecules = 1).")
+                batch = [mol2graph(mols=b, atom_features_batch=atom_features_batch,
+                                   bond_features_batch=bond_features_batch,
+                                   overwrite_default_atom_features=self.overwrite_default_atom_features,
+                                   overwrite_default_bond_features=self.overwrite_default_bond_features)
+                         for b in batch]
+            else:
+                batch = [mol2graph(b) for b in batch]
+        if self.use_input_features:                                 # mpn.py:266-270
+            features_batch = torch.from_numpy(np.stack(features_batch)).float().to(self.device)
+            if self.features_only:
+                return features_batch
+        if self.atom_descriptors == "descriptor":
+            raise NotImplementedError("atom_descriptors='descriptor' is not accelerated by the B200 encoder")
+        encodings = [enc(ba) for enc, ba in zip(self.encoder, batch)]          # :279
+        output = reduce(lambda x, y: torch.cat((x, y), dim=1), encodings)      # :281
+        if self.use_input_features:                                 # :283-287
+            if len(features_batch.shape) == 1:
+                features_batch = features_batch.view(1, -1)
+            output = torch.cat([output, features_batch.to(output.device)], dim=1)
+        return output
+
+
+def install():
+    """Monkey-patches an importable chemprop so MoleculeModel builds this MPN
+    (chemprop/models/model.py:8 did ``from .mpn import MPN``)."""
+    import chemprop.models.model as cm
+    import chemprop.models.mpn as cmpn
+    cmpn.MPN, cmpn.MPNEncoder = MPN, MPNEncoder
+    cm.MPN = MPN

@@ -1,0 +1,163 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the reference's golden
+vectors and against the CPU oracle on seeded synthetic inputs.
+
+Tolerances (BASELINE.json north_star): indices bit-exact; FP32 path <= 1e-5 relative on the
+encoder output (||x-ref||_F / ||ref||_F), <= 1e-4 on gradients (summation order differs)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import _golden
+import _util
+from oracle import mpn_oracle
+from polymer_chemprop_b200 import BatchMolGraph, DeviceGraph, _capi, synth
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda", 0)
+OUT_TOL, GRAD_TOL = 1e-5, 1e-4
+
+
+def _check_csr(components):
+    g = _util.ComponentsGraph(components)
+    dg = DeviceGraph(g, DEV)
+    a2b, b2a, b2revb = components[4], components[5], components[6]
+    in_ptr, in_idx, out_ptr, out_idx, dst = mpn_oracle.csr_from_a2b(a2b.tolist(), b2a.tolist(), b2revb.tolist())
+    nb1 = b2a.numel() - 1
+    assert np.array_equal(dg.in_ptr.cpu().numpy(), in_ptr)
+    assert np.array_equal(dg.in_ptr.cpu().numpy(), out_ptr)          # out-degree == in-degree
+    assert np.array_equal(dg.in_idx.cpu().numpy()[:nb1], in_idx)
+    assert np.array_equal(dg.out_idx.cpu().numpy()[:nb1], out_idx)
+    assert np.array_equal(dg.dst.cpu().numpy(), dst)
+    assert np.array_equal(dg.src.cpu().numpy(), b2a.numpy().astype(np.int32))
+    assert np.array_equal(dg.rev.cpu().numpy(), b2revb.numpy().astype(np.int32))
+    mol_of = np.full(a2b.shape[0], -1, np.int32)
+    for i, (s, n) in enumerate(components[7]):
+        mol_of[s:s + n] = i
+    assert np.array_equal(dg.mol_of.cpu().numpy(), mol_of)
+    flags = dg.flags.cpu().numpy()
+    assert flags[0] == 0 and flags[1] == max(1, int((a2b != 0).sum(1).max())) or flags[1] == int((a2b != 0).sum(1).max())
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_csr_bit_exact_golden(name):
+    _check_csr(_golden.load(name)["components"])
+
+
+def test_csr_bit_exact_large():
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 700, 5) + [synth.empty_graph()] +
+                        synth.make_graphs("qm9", 300, 6))
+    _check_csr(bmg.get_components())
+
+
+def test_csr_rejects_inconsistent_graph():
+    comps = list(_golden.load("copoly_b2")["components"])
+    b2revb = comps[6].clone()
+    b2revb[3], b2revb[4] = b2revb[5].item(), b2revb[6].item()       # break the involution
+    comps[6] = b2revb
+    with pytest.raises(ValueError):
+        DeviceGraph(_util.ComponentsGraph(tuple(comps)), DEV)
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_encoder_matches_reference_golden_fp32(name):
+    g = _golden.load(name)
+    model = _util.model_from_params(g["params"], g["cfg"])
+    out, grads = _util.run_fwd_bwd(model, _util.ComponentsGraph(g["components"]), g["d_out"])
+    assert out.shape == g["out"].shape
+    assert _golden.rel_err(out, g["out"]) <= OUT_TOL
+    assert set(grads) == set(g["grads"])
+    for k, ref in g["grads"].items():
+        assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
+
+
+@pytest.mark.parametrize("activation", ["ReLU", "LeakyReLU", "tanh", "SELU", "ELU"])
+@pytest.mark.parametrize("undirected,bias", [(False, False), (True, True)])
+def test_encoder_matches_oracle_synthetic(activation, undirected, bias):
+    """Seeded synthetic batch, odd hidden size, every supported activation."""
+    graphs = synth.make_graphs("copolymer", 24, 21, dense_features=True, random_edge_weights=True)
+    bmg = BatchMolGraph(graphs + [synth.empty_graph()])
+    cfg = dict(hidden_size=76, depth=4, activation=activation, undirected=undirected, bias=bias,
+               aggregation="mean")
+    torch.manual_seed(5)
+    model = _util.MPN(_util.make_args(**cfg), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)
+    for p in model.parameters():
+        if p.requires_grad:
+            torch.nn.init.normal_(p, 0.0, 0.1) if p.dim() == 1 else torch.nn.init.xavier_normal_(p)
+    d_out = torch.randn(len(bmg.a_scope), 76, generator=torch.Generator().manual_seed(9))
+    out, grads = _util.run_fwd_bwd(model, bmg, d_out)
+    weights = {k: v.detach().cpu() for k, v in model.encoder[0].state_dict().items() if k != "cached_zero_vector"}
+    ref_out, ref_grads = mpn_oracle.encoder_forward_backward(
+        bmg.get_components(), weights, d_out, depth=4, activation=activation, undirected=undirected)
+    assert _golden.rel_err(out, ref_out) <= OUT_TOL
+    for k, ref in ref_grads.items():
+        assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
+
+
+def test_backward_is_bitwise_deterministic():
+    g = _golden.load("copoly_b50")
+    model = _util.model_from_params(g["params"], g["cfg"])
+    graph = _util.ComponentsGraph(g["components"])
+    out1, grads1 = _util.run_fwd_bwd(model, graph, g["d_out"])
+    out2, grads2 = _util.run_fwd_bwd(model, graph, g["d_out"])
+    assert torch.equal(out1, out2)
+    for k in grads1:
+        assert torch.equal(grads1[k], grads2[k]), k
+
+
+def test_host_buffer_entry_point_matches_golden():
+    """wd_encoder_host: the reference's own calling convention (CPU tensors in, mpn.py:81-87)."""
+    g = _golden.load("copoly_b8_randw")
+    fa, fb, wa, wb, a2b, b2a, b2revb, a_scope, _bs, dop = g["components"]
+    cfg, P = g["cfg"], g["params"]
+    h = cfg["hidden_size"]
+    c = _capi.WdConfig(h, fa.shape[1], fb.shape[1], cfg["depth"], 0, 0, 0, 0, 0, 100.0)
+    scope = torch.tensor(a_scope, dtype=torch.int64).contiguous()
+    dopt = torch.tensor(dop, dtype=torch.float64)
+    out = torch.empty(len(a_scope), h)
+    grads = {k: torch.empty_like(v) for k, v in P.items() if k != "cached_zero_vector"}
+    w = _capi.WdWeights(P["W_i.weight"].data_ptr(), None, P["W_h.weight"].data_ptr(), None,
+                        P["W_o.weight"].data_ptr(), P["W_o.bias"].data_ptr())
+    gr = _capi.WdGrads(grads["W_i.weight"].data_ptr(), None, grads["W_h.weight"].data_ptr(), None,
+                       grads["W_o.weight"].data_ptr(), grads["W_o.bias"].data_ptr())
+    torch.cuda.init()
+    rc = _capi.lib().wd_encoder_host(fa.data_ptr(), fb.data_ptr(), wa.data_ptr(), wb.data_ptr(), a2b.data_ptr(),
+                                     b2a.data_ptr(), b2revb.data_ptr(), scope.data_ptr(), dopt.data_ptr(),
+                                     fa.shape[0], fb.shape[0], a2b.shape[1], len(a_scope), C.byref(w),
+                                     C.byref(c), out.data_ptr(), g["d_out"].data_ptr(), C.byref(gr), None)
+    _capi.check(rc)
+    assert _golden.rel_err(out, g["out"]) <= OUT_TOL
+    for k, ref in g["grads"].items():
+        assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
+
+
+def test_full_size_properties_b4096():
+    """BASELINE config 2 at full size (B=4096, h=300, d=3): size-independent properties.
+    (1) batch-permutation equivariance of the readout rows; (2) molecules are independent, so the
+    first 64 rows equal the encoder run on those 64 graphs alone; (3) gradients of a sum over
+    disjoint halves add up (linearity of the backward in d_out)."""
+    graphs = synth.make_graphs("copolymer", 4096, 0)
+    torch.manual_seed(0)
+    bmg = BatchMolGraph(graphs)
+    model = _util.MPN(_util.make_args(), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)
+    for p in model.parameters():
+        if p.requires_grad and p.dim() == 2:
+            torch.nn.init.xavier_normal_(p)
+    with torch.no_grad():
+        out = model([bmg]).cpu()
+        small = model([BatchMolGraph(graphs[:64])]).cpu()
+        perm = np.random.default_rng(0).permutation(4096)
+        out_p = model([BatchMolGraph([graphs[i] for i in perm])]).cpu()
+    assert torch.isfinite(out).all()
+    assert _golden.rel_err(out[:64], small) <= 1e-6
+    assert _golden.rel_err(out_p, out[perm]) <= 1e-6
+    d = torch.randn(4096, 300, generator=torch.Generator().manual_seed(1))
+    d1, d2 = d.clone(), d.clone()
+    d1[2048:] = 0
+    d2[:2048] = 0
+    _, g = _util.run_fwd_bwd(model, bmg, d)
+    _, g1 = _util.run_fwd_bwd(model, bmg, d1)
+    _, g2 = _util.run_fwd_bwd(model, bmg, d2)
+    for k in g:
+        assert _golden.rel_err(g1[k] + g2[k], g[k]) <= 1e-5, k
