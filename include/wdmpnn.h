@@ -157,6 +157,18 @@ void wd_profile_reset(void);    /* forget recorded launches (keeps the event poo
 /* Synchronises the recorded events and returns total milliseconds and launch count of category. */
 int wd_profile_read(int category, double* total_ms, int64_t* launches);
 
+/* Test hooks: the raw contractions behind the encoder on plain row-major operands, so that the
+ * tensor-core kernels can be checked in isolation (tests/test_gpu_contractions.py).
+ * wd_debug_gemm: C[M, ldc] = epi(A[M,K] * B^T + bias (+ R)); B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k];
+ *   epi 0 = store, 1 = ReLU, 2 = ReLU(R + .).  Columns [N, ldc) of C are zero-filled.
+ *   TF32 mode needs `scratch` >= 4 * round_up(N,304-ish tiles) * round_up(K,32) bytes (packed weights).
+ * wd_debug_dw: out[N1, N2] = X[R, :N1]^T * Y[R, :N2]; `scratch` >= 64 * N1 * N2 * 4 bytes (partials). */
+int wd_debug_gemm(const float* A, int lda, const float* W, int ldb, int b_kn, const float* bias,
+                  const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, int epi,
+                  int math_mode, void* scratch, size_t scratch_bytes, void* stream);
+int wd_debug_dw(const float* X, int ldx, const float* Y, int ldy, float* out, int64_t R, int N1, int N2,
+                int math_mode, void* scratch, size_t scratch_bytes, void* stream);
+
 /* Thread-local message of the last failing call on this thread. */
 const char* wd_last_error(void);
 /* Kernel launches issued by this library since load (for bench.py's gpu_launches). */

@@ -5,6 +5,7 @@
 #include "graph_kernels.cuh"
 #include "operands.cuh"
 #include "simt_gemm.cuh"
+#include "tc_host.cuh"
 
 namespace wd {
 
@@ -18,7 +19,10 @@ struct Layout {
   int ldh;                 // row stride of every [*, h] activation buffer (h rounded up to 4)
   int64_t szB, szA;        // floats per [N_b, ldh] / [N_a, ldh] buffer
   int64_t I, M, Agg, H, mscale, U, dZ, dS, dI, dA, dZo, partials, total;
-  int Z;                   // row chunks of the weight-gradient contractions
+  int Z;                   // max row chunks of the weight-gradient contractions (sizes `partials`)
+  int Zh, Zi, Zo;          // row chunks of the dW_h / dW_i / dW_o contractions
+  TcPacked pWi, pWh, pWo, pWhT, pWoT;   // TF32 mode: packed weight images (img == offset holder until bound)
+  int64_t pk[5];           // offsets of the five packed images
   float* p(void* ws, int64_t off) const { return reinterpret_cast<float*>(ws) + off; }
 };
 
@@ -49,10 +53,26 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   L.dA = take(L.szA);
   L.dZo = take(L.szA);
   const int Fo = c.atom_fdim + h;
-  L.Z = std::max(std::max(dw_chunks(Nb, h, h), dw_chunks(Nb, h, c.bond_fdim)), dw_chunks(Na, h, Fo));
+  if (c.math_mode == WD_MATH_TF32) {
+    L.Zh = tc_dw_z(Nb, h, tc_dw_count_tiles(h, 0));
+    L.Zi = tc_dw_z(Nb, h, tc_dw_count_tiles(c.bond_fdim, 0));
+    L.Zo = tc_dw_z(Na, h, tc_dw_count_tiles(c.atom_fdim, h));
+  } else {
+    L.Zh = dw_chunks(Nb, h, h);
+    L.Zi = dw_chunks(Nb, h, c.bond_fdim);
+    L.Zo = dw_chunks(Na, h, Fo);
+  }
+  L.Z = std::max(std::max(L.Zh, L.Zi), L.Zo);
   int64_t pw = std::max<int64_t>((int64_t)std::max(1, c.depth - 1) * h * h,
                                  (int64_t)h * std::max(Fo, c.bond_fdim));
   L.partials = take((int64_t)L.Z * pw + (int64_t)L.Z * h);
+  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0);     // I = f_bonds W_i^T
+  L.pWh = tc_packed_geometry(h, h, 0);               // S W_h^T
+  L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
+  L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h
+  L.pWoT = tc_packed_geometry(h, h, 0);              // dA_d = dZo W_o[:, F_a:]
+  const TcPacked* pk[5] = {&L.pWi, &L.pWh, &L.pWo, &L.pWhT, &L.pWoT};
+  for (int i = 0; i < 5; ++i) L.pk[i] = take(c.math_mode == WD_MATH_TF32 ? pk[i]->floats() : 0);
   L.total = off;
   return L;
 }
@@ -86,23 +106,33 @@ int check_graph(const WdGraph* g, const WdWeights* w, const WdConfig* c) {
 
 inline int grid1d(int64_t n, int block = 256) { return (int)ceil_div(std::max<int64_t>(n, 1), block); }
 
-// ---- contraction dispatch: FP32 SIMT today; TF32 tcgen05 kernels plug in here -------------
+// ---- contraction dispatch: FP32 -> SIMT FFMA kernels, TF32 -> tcgen05 kernels (tc == packed weights) ----
 template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
 int gemm(const WdConfig& c, cudaStream_t s, const AOperand& A, const float* W, int ldb, const float* bias,
-         const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K) {
+         const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, const TcPacked* tc) {
+  if (c.math_mode == WD_MATH_TF32) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M);
   dim3 grid((unsigned)ceil_div(M, SG_BM), (unsigned)ceil_div(std::max(N, ldc), SG_BN));
   WD_LAUNCH((k_simt_gemm<AMODE, BMODE, EPI, ACT, PREACT>), grid, SG_THREADS, 0, s, A, W, ldb, bias, R, ldr,
             C, ldc, M, N, K);
   return WD_OK;
 }
 
-// P[z_off .. z_off+Z) <- partial X^T Y over row chunks
+// P[0 .. Z) <- partial X^T Y over Z row chunks; Y has w0 (+ w1 for CONCAT) columns
 template <int YMODE, int ACT, bool PREACT>
-int dw_partial(cudaStream_t s, const float* X, int ldx, const AOperand& Y, float* P, int64_t R, int N1,
-               int N2, int Z) {
+int dw_partial(const WdConfig& c, cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1,
+               float* P, int64_t R, int N1, int Z) {
+  if (c.math_mode == WD_MATH_TF32) return tc_dw<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
+  const int N2 = w0 + w1;
   int64_t rpc = round_up(ceil_div(R, Z), DW_BK);
   dim3 grid((unsigned)ceil_div(N2, DW_BN), (unsigned)ceil_div(N1, DW_BM), (unsigned)Z);
   WD_LAUNCH((k_simt_dw<YMODE, ACT, PREACT>), grid, DW_THREADS, 0, s, X, ldx, Y, P, R, N1, N2, rpc);
+  return WD_OK;
+}
+
+// TF32 mode: bind the packed-weight images to the workspace and (re)pack them from the live weights
+int bind_packed(const WdConfig& c, Layout& L, void* ws) {
+  TcPacked* pk[5] = {&L.pWi, &L.pWh, &L.pWo, &L.pWhT, &L.pWoT};
+  for (int i = 0; i < 5; ++i) pk[i]->img = c.math_mode == WD_MATH_TF32 ? L.p(ws, L.pk[i]) : nullptr;
   return WD_OK;
 }
 
@@ -123,15 +153,22 @@ int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_
 template <int ACT>
 int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, float* out,
                  cudaStream_t s) {
-  const Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
+  Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
   const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim;
   const int64_t Na = g.n_atoms, Nb = g.n_bonds, G = g.n_mols;
   float* I = L.p(ws, L.I);
+  bind_packed(c, L, ws);
+  if (c.math_mode == WD_MATH_TF32) {   // weights change every step: repack (tiny) on the stream
+    ProfScope ps(WD_PROF_MISC);
+    WD_TRY(tc_pack(s, w.W_i, Fb, B_NK, L.pWi));
+    if (c.depth > 1) WD_TRY(tc_pack(s, w.W_h, h, B_NK, L.pWh));
+    WD_TRY(tc_pack(s, w.W_o, Fa + h, B_NK, L.pWo));
+  }
   // input = W_i(f_bonds)                                                      mpn.py:96
   AOperand a_in{g.f_bonds, nullptr, nullptr, nullptr, Fb, 0, 0};
   { ProfScope ps(WD_PROF_INPUT_PROJ);
   WD_TRY((gemm<A_PLAIN, B_NK, E_STORE, ACT, false>(c, s, a_in, w.W_i, Fb, c.bias ? w.b_i : nullptr, nullptr, 0,
-                                                  I, ld, Nb, h, Fb))); }
+                                                  I, ld, Nb, h, Fb, &L.pWi))); }
   const float* prev = I;   // message = act(input) is applied on load (PREACT)          :97
   for (int t = 1; t < c.depth; ++t) {                                               // :100
     const bool pre = (t == 1);
@@ -154,8 +191,8 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
     AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
     const float* bh = c.bias ? w.b_h : nullptr;
-    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h)));
-    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h)));
+    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh)));
+    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh)));
     prev = M_t;
   }
   // final aggregate + atom update                                                    :127-134
@@ -166,7 +203,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   float* H = L.p(ws, L.H);
   AOperand a_o{g.f_atoms, A_d, nullptr, nullptr, Fa, ld, Fa};
   { ProfScope ps(WD_PROF_ATOM_UPDATE);
-  WD_TRY((gemm<A_CONCAT, B_NK, E_ACT, ACT, false>(c, s, a_o, w.W_o, Fa + h, w.b_o, nullptr, 0, H, ld, Na, h, Fa + h))); }
+  WD_TRY((gemm<A_CONCAT, B_NK, E_ACT, ACT, false>(c, s, a_o, w.W_o, Fa + h, w.b_o, nullptr, 0, H, ld, Na, h, Fa + h, &L.pWo))); }
   // readout                                                                          :146-171
   if (G > 0) {
     ProfScope ps(WD_PROF_READOUT);
@@ -197,8 +234,14 @@ int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const floa
 template <int ACT>
 int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, const float* d_out,
                   const WdGrads& gr, cudaStream_t s) {
-  const Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
+  Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
   const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim, Fo = Fa + h;
+  bind_packed(c, L, ws);
+  if (c.math_mode == WD_MATH_TF32) {
+    ProfScope ps(WD_PROF_MISC);
+    if (c.depth > 1) WD_TRY(tc_pack(s, w.W_h, h, B_KN, L.pWhT));
+    WD_TRY(tc_pack(s, w.W_o + Fa, Fo, B_KN, L.pWoT));
+  }
   const int64_t Na = g.n_atoms, Nb = g.n_bonds;
   const int d = c.depth;
   float *I = L.p(ws, L.I), *H = L.p(ws, L.H), *dZ = L.p(ws, L.dZ), *dS = L.p(ws, L.dS), *dI = L.p(ws, L.dI),
@@ -213,18 +256,18 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
             L.p(ws, L.mscale), dZo, Na); }
   {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
-    const int Z = dw_chunks(Na, h, Fo);
+    const int Z = L.Zo;
     AOperand y{g.f_atoms, A_d, nullptr, nullptr, Fa, ld, Fa};
-    WD_TRY((dw_partial<A_CONCAT, ACT, false>(s, dZo, ld, y, P, Na, h, Fo, Z)));
+    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, P, Na, h, Z)));
     WD_TRY(reduce_partials(s, P, gr.dW_o, (int64_t)h * Fo, Z));
     WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, Z));
   }
   // dA_d = dZo * W_o[:, F_a:]
   AOperand a_zo{dZo, nullptr, nullptr, nullptr, ld, 0, 0};
   { ProfScope ps(WD_PROF_DX);
-  WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_zo, w.W_o + Fa, Fo, nullptr, nullptr, 0, dA, ld, Na, h, h))); }
+  WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_zo, w.W_o + Fa, Fo, nullptr, nullptr, 0, dA, ld, Na, h, h, &L.pWoT))); }
 
-  const int Zh = dw_chunks(Nb, h, h);
+  const int Zh = L.Zh;
   for (int t = d - 1; t >= 1; --t) {
     const float* M_t = L.p(ws, L.M) + (int64_t)(t - 1) * L.szB;
     const float* A_t = L.p(ws, L.Agg) + (int64_t)(t - 1) * L.szA;
@@ -246,12 +289,12 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     AOperand y{A_t, u, g.src, g.rev, ld, ld, 0};
     float* Pt = P + (int64_t)(d - 1 - t) * Zh * h * h;
     { ProfScope ps(WD_PROF_DW);
-    if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(s, dZ, ld, y, Pt, Nb, h, h, Zh)));
-    else      WD_TRY((dw_partial<A_GATHER_DIFF, ACT, false>(s, dZ, ld, y, Pt, Nb, h, h, Zh))); }
+    if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh)));
+    else      WD_TRY((dw_partial<A_GATHER_DIFF, ACT, false>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh))); }
     // dS = dZ_t * W_h ; dA[a] = sum over out-edges of a of dS  (transpose-CSR, no atomics)
     AOperand a_z{dZ, nullptr, nullptr, nullptr, ld, 0, 0};
     { ProfScope ps(WD_PROF_DX);
-    WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_z, w.W_h, h, nullptr, nullptr, 0, dS, ld, Nb, h, h))); }
+    WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_z, w.W_h, h, nullptr, nullptr, 0, dS, ld, Nb, h, h, &L.pWhT))); }
     ProfScope ps(WD_PROF_SCATTER);
     WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, dS, ld, nullptr, g.in_ptr, g.out_idx, dA, Na, nc4);
   }
@@ -267,9 +310,9 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   }
   {  // dW_i = dI^T f_bonds ; db_i = colsum(dI)
     ProfScope ps(WD_PROF_DW);
-    const int Z = dw_chunks(Nb, h, Fb);
+    const int Z = L.Zi;
     AOperand y{g.f_bonds, nullptr, nullptr, nullptr, Fb, 0, 0};
-    WD_TRY((dw_partial<A_PLAIN, ACT, false>(s, dI, ld, y, P, Nb, h, Fb, Z)));
+    WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s, dI, ld, y, Fb, 0, P, Nb, h, Z)));
     WD_TRY(reduce_partials(s, P, gr.dW_i, (int64_t)h * Fb, Z));
     if (c.bias && gr.db_i) WD_TRY(colsum(s, dI, ld, Pcol, gr.db_i, Nb, h, Z));
   }
@@ -321,3 +364,51 @@ extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weight
 extern "C" const char* wd_last_error(void) { return wd::g_err; }
 extern "C" int64_t wd_launch_count(void) { return wd::g_launches.load(); }
 extern "C" int wd_abi_version(void) { return 1; }
+
+// ---- test hooks: the raw contractions behind the encoder, on plain operands ----------------------
+// C[M, ldc] = epi(A[M, K] * B^T (+ bias) (+ R)), B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k].
+// epi: 0 store, 1 ReLU, 2 ReLU(R + .).  `scratch` holds the packed weight image in TF32 mode.
+extern "C" int wd_debug_gemm(const float* A, int lda, const float* W, int ldb, int b_kn, const float* bias,
+                             const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, int epi,
+                             int math_mode, void* scratch, size_t scratch_bytes, void* stream) {
+  using namespace wd;
+  cudaStream_t s = (cudaStream_t)stream;
+  WdConfig c{};
+  c.math_mode = math_mode;
+  TcPacked pk = tc_packed_geometry(N, K, 0);
+  if (math_mode == WD_MATH_TF32) {
+    if (!scratch || scratch_bytes < (size_t)pk.floats() * sizeof(float))
+      return fail(WD_ERR_INVALID_ARG, "wd_debug_gemm: scratch needs %lld bytes", (long long)pk.floats() * 4);
+    pk.img = reinterpret_cast<float*>(scratch);
+    WD_TRY(tc_pack(s, W, ldb, b_kn ? B_KN : B_NK, pk));
+  }
+  AOperand a{A, nullptr, nullptr, nullptr, lda, 0, K};
+  constexpr int ACT = WD_ACT_RELU;
+  if (b_kn) {
+    if (epi != 0) return fail(WD_ERR_UNSUPPORTED, "wd_debug_gemm: b_kn supports epi 0 only");
+    return gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a, W, ldb, bias, R, ldr, C, ldc, M, N, K, &pk);
+  }
+  switch (epi) {
+    case 0: return gemm<A_PLAIN, B_NK, E_STORE, ACT, false>(c, s, a, W, ldb, bias, R, ldr, C, ldc, M, N, K, &pk);
+    case 1: return gemm<A_PLAIN, B_NK, E_ACT, ACT, false>(c, s, a, W, ldb, bias, R, ldr, C, ldc, M, N, K, &pk);
+    case 2: return gemm<A_PLAIN, B_NK, E_RES_ACT, ACT, false>(c, s, a, W, ldb, bias, R, ldr, C, ldc, M, N, K, &pk);
+  }
+  return fail(WD_ERR_INVALID_ARG, "wd_debug_gemm: epi %d unknown", epi);
+}
+
+// out[N1, N2] = X[R, :N1]^T * Y[R, :N2]  (deterministic split over rows + fixed-order reduction).
+// `scratch` holds the row-chunk partials.
+extern "C" int wd_debug_dw(const float* X, int ldx, const float* Y, int ldy, float* out, int64_t R, int N1, int N2,
+                           int math_mode, void* scratch, size_t scratch_bytes, void* stream) {
+  using namespace wd;
+  cudaStream_t s = (cudaStream_t)stream;
+  WdConfig c{};
+  c.math_mode = math_mode;
+  const int Z = math_mode == WD_MATH_TF32 ? tc_dw_z(R, N1, tc_dw_count_tiles(N2, 0)) : dw_chunks(R, N1, N2);
+  if (!scratch || scratch_bytes < (size_t)Z * N1 * N2 * sizeof(float))
+    return fail(WD_ERR_INVALID_ARG, "wd_debug_dw: scratch needs %lld bytes", (long long)Z * N1 * N2 * 4);
+  float* P = reinterpret_cast<float*>(scratch);
+  AOperand y{Y, nullptr, nullptr, nullptr, ldy, 0, 0};
+  WD_TRY((dw_partial<A_PLAIN, WD_ACT_RELU, false>(c, s, X, ldx, y, N2, 0, P, R, N1, Z)));
+  return reduce_partials(s, P, out, (int64_t)N1 * N2, Z);
+}

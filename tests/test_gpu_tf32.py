@@ -1,0 +1,136 @@
+"""GPU parity of the tcgen05 (TF32) path: the raw contractions against fp64 torch products, and the
+encoder against the reference's golden vectors / the CPU oracle.
+
+Tolerances (BASELINE.json north_star): TF32 tensor-core path <= 1e-3 relative on the encoder output
+(||x-ref||_F / ||ref||_F); gradients are held to 1e-2 (they pass through 2x more contractions)."""
+import numpy as np
+import pytest
+import torch
+
+import _golden
+import _util
+from oracle import mpn_oracle
+from polymer_chemprop_b200 import BatchMolGraph, _capi, synth
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda", 0)
+OUT_TOL, GRAD_TOL, GEMM_TOL = 1e-3, 1e-2, 1e-3
+
+
+def _gemm(A, W, N, K, b_kn=False, bias=None, R=None, epi=0, mode=1):
+    L, p = _capi.lib(), _capi.ptr
+    M, ldc = A.shape[0], (N + 3) // 4 * 4
+    C = torch.full((M, ldc), float("nan"), device=DEV)
+    scratch = torch.empty(4 * (N + 320) * (K + 64) + 1024, dtype=torch.uint8, device=DEV)
+    _capi.check(L.wd_debug_gemm(p(A), A.stride(0), p(W), W.stride(0), int(b_kn), p(bias), p(R),
+                                R.stride(0) if R is not None else 0, p(C), ldc, M, N, K, epi, mode, p(scratch),
+                                scratch.numel(), _capi.current_stream(DEV)))
+    torch.cuda.synchronize()
+    return C
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 16, 32), (100, 48, 40), (256, 64, 96), (1000, 300, 300), (1000, 300, 147),
+                                   (3000, 301, 433), (20000, 300, 300), (700, 640, 200), (2000, 2400, 512)])
+def test_tc_gemm_matches_fp64(M, N, K):
+    g = torch.Generator(device=DEV).manual_seed(M + N + K)
+    A = torch.randn(M, K, device=DEV, generator=g)
+    W = torch.randn(N, K, device=DEV, generator=g) / K ** 0.5
+    C = _gemm(A, W, N, K)
+    ref = A.double() @ W.double().t()
+    assert _golden.rel_err(C[:, :N].cpu(), ref.cpu()) <= GEMM_TOL
+    assert bool((C[:, N:] == 0).all())            # pad columns [N, ldc) are kept at zero
+
+
+def test_tc_gemm_transposed_weights_and_epilogues():
+    g = torch.Generator(device=DEV).manual_seed(3)
+    M, N, K = 1500, 300, 300
+    A = torch.randn(M, K, device=DEV, generator=g)
+    W = torch.randn(K, N, device=DEV, generator=g) / K ** 0.5
+    C = _gemm(A, W, N, K, b_kn=True)
+    assert _golden.rel_err(C[:, :N].cpu(), (A.double() @ W.double()).cpu()) <= GEMM_TOL
+    Wn = torch.randn(N, K, device=DEV, generator=g) / K ** 0.5
+    b = torch.randn(N, device=DEV, generator=g)
+    R = torch.randn(M, N, device=DEV, generator=g)
+    ref = A.double() @ Wn.double().t() + b.double()
+    C1 = _gemm(A, Wn, N, K, bias=b, epi=1)
+    assert _golden.rel_err(C1[:, :N].cpu(), ref.clamp_min(0).cpu()) <= GEMM_TOL
+    C2 = _gemm(A, Wn, N, K, bias=b, R=R, epi=2)
+    assert _golden.rel_err(C2[:, :N].cpu(), (ref + R.double()).clamp_min(0).cpu()) <= GEMM_TOL
+
+
+@pytest.mark.parametrize("R,N1,N2", [(1000, 64, 64), (4100, 128, 32), (10000, 300, 300), (5000, 300, 147),
+                                     (50000, 300, 433), (3000, 640, 700)])
+def test_tc_dw_matches_fp64(R, N1, N2):
+    L, p = _capi.lib(), _capi.ptr
+    g = torch.Generator(device=DEV).manual_seed(R + N1 + N2)
+    ld1 = (N1 + 3) // 4 * 4
+    X = torch.randn(R, ld1, device=DEV, generator=g)
+    Y = torch.randn(R, N2, device=DEV, generator=g)
+    out = torch.full((N1, N2), float("nan"), device=DEV)
+    scratch = torch.empty(64 * N1 * N2 * 4, dtype=torch.uint8, device=DEV)
+    _capi.check(L.wd_debug_dw(p(X), ld1, p(Y), N2, p(out), R, N1, N2, 1, p(scratch), scratch.numel(),
+                              _capi.current_stream(DEV)))
+    torch.cuda.synchronize()
+    ref = X[:, :N1].double().t() @ Y.double()
+    assert _golden.rel_err(out.cpu(), ref.cpu()) <= GEMM_TOL
+
+
+@pytest.mark.parametrize("name", _golden.NAMES)
+def test_encoder_tf32_matches_reference_golden(name):
+    g = _golden.load(name)
+    model = _util.model_from_params(g["params"], g["cfg"], math_mode="tf32")
+    out, grads = _util.run_fwd_bwd(model, _util.ComponentsGraph(g["components"]), g["d_out"])
+    assert out.shape == g["out"].shape
+    assert _golden.rel_err(out, g["out"]) <= OUT_TOL
+    for k, ref in g["grads"].items():
+        assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
+
+
+@pytest.mark.parametrize("hidden,depth,undirected,bias", [(76, 4, False, False), (301, 3, True, True), (640, 2, False, True)])
+def test_encoder_tf32_matches_oracle_synthetic(hidden, depth, undirected, bias):
+    graphs = synth.make_graphs("copolymer", 40, 21, dense_features=True, random_edge_weights=True)
+    bmg = BatchMolGraph(graphs + [synth.empty_graph()])
+    cfg = dict(hidden_size=hidden, depth=depth, undirected=undirected, bias=bias)
+    torch.manual_seed(5)
+    model = _util.MPN(_util.make_args(wd_math_mode="tf32", **cfg), atom_fdim=bmg.atom_fdim,
+                      bond_fdim=bmg.bond_fdim).to(DEV)
+    for p in model.parameters():
+        if p.requires_grad:
+            torch.nn.init.normal_(p, 0.0, 0.1) if p.dim() == 1 else torch.nn.init.xavier_normal_(p)
+    d_out = torch.randn(len(bmg.a_scope), hidden, generator=torch.Generator().manual_seed(9))
+    out, grads = _util.run_fwd_bwd(model, bmg, d_out)
+    weights = {k: v.detach().cpu() for k, v in model.encoder[0].state_dict().items() if k != "cached_zero_vector"}
+    ref_out, ref_grads = mpn_oracle.encoder_forward_backward(bmg.get_components(), weights, d_out, depth=depth,
+                                                             undirected=undirected)
+    assert _golden.rel_err(out, ref_out) <= OUT_TOL
+    for k, ref in ref_grads.items():
+        assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
+
+
+def test_tf32_backward_is_bitwise_deterministic():
+    g = _golden.load("copoly_b50")
+    model = _util.model_from_params(g["params"], g["cfg"], math_mode="tf32")
+    graph = _util.ComponentsGraph(g["components"])
+    out1, grads1 = _util.run_fwd_bwd(model, graph, g["d_out"])
+    out2, grads2 = _util.run_fwd_bwd(model, graph, g["d_out"])
+    assert torch.equal(out1, out2)
+    for k in grads1:
+        assert torch.equal(grads1[k], grads2[k]), k
+
+
+def test_tf32_full_size_b4096_close_to_fp32_path():
+    """BASELINE config 2 at full size: the TF32 path against the (oracle-pinned) FP32 CUDA path."""
+    graphs = synth.make_graphs("copolymer", 4096, 0)
+    bmg = BatchMolGraph(graphs)
+    outs = {}
+    for mode in ("fp32", "tf32"):
+        torch.manual_seed(0)
+        model = _util.MPN(_util.make_args(wd_math_mode=mode), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)
+        for p in model.parameters():
+            if p.requires_grad and p.dim() == 2:
+                torch.nn.init.xavier_normal_(p)
+        d = torch.randn(4096, 300, generator=torch.Generator().manual_seed(1))
+        outs[mode] = _util.run_fwd_bwd(model, bmg, d)
+    assert _golden.rel_err(outs["tf32"][0], outs["fp32"][0]) <= OUT_TOL
+    for k, ref in outs["fp32"][1].items():
+        assert _golden.rel_err(outs["tf32"][1][k], ref) <= GRAD_TOL, k
