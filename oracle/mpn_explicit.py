@@ -21,8 +21,22 @@ def _aggregate(M, w_bonds, in_ptr, in_idx):
     return A
 
 
+def tf32_round(x):
+    """Round-to-nearest (ties away) of fp32 values to the 10-bit TF32 mantissa -- what the CUDA
+    path's producers apply (cvt.rna.tf32.f32) before tcgen05.mma kind::tf32."""
+    u = np.asarray(x, np.float32).view(np.uint32).astype(np.uint64)
+    u = ((u + 0x1000) & 0xFFFFE000).astype(np.uint32)
+    return u.view(np.float32).astype(np.float64)
+
+
+def mm_tf32(a, b):
+    """Matrix product with both operands rounded to TF32 and exact (f64) accumulation: the
+    error model of the tensor-core path, used to attribute its tolerance."""
+    return tf32_round(a) @ tf32_round(b)
+
+
 def forward_backward(components, weights, d_out, depth, undirected=False,
-                     aggregation="mean", aggregation_norm=100.0):
+                     aggregation="mean", aggregation_norm=100.0, mm=np.matmul):
     f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, a_scope, _bs, dop = components
     f64 = np.float64
     f_atoms, f_bonds = np.asarray(f_atoms, f64), np.asarray(f_bonds, f64)
@@ -37,7 +51,7 @@ def forward_backward(components, weights, d_out, depth, undirected=False,
     Fa, h, G = f_atoms.shape[1], Wh.shape[0], len(a_scope)
 
     # ---- forward ----
-    I = f_bonds @ Wi.T + (bi if bi is not None else 0.0)
+    I = mm(f_bonds, Wi.T) + (bi if bi is not None else 0.0)
     Ms = [np.maximum(I, 0.0)]          # M_0 .. M_{d-1}
     Us, Ss = [], []                    # U_t = (undirected-symmetrised) input of step t, S_t
     for _ in range(depth - 1):
@@ -48,10 +62,10 @@ def forward_backward(components, weights, d_out, depth, undirected=False,
         S = A[b2a] - U[b2revb]
         Us.append(U)
         Ss.append(S)
-        Ms.append(np.maximum(I + S @ Wh.T + (bh if bh is not None else 0.0), 0.0))
+        Ms.append(np.maximum(I + mm(S, Wh.T) + (bh if bh is not None else 0.0), 0.0))
     A_d = _aggregate(Ms[-1], w_bonds, in_ptr, in_idx)
     X = np.concatenate([f_atoms, A_d], axis=1)
-    H = np.maximum(X @ Wo.T + bo, 0.0)
+    H = np.maximum(mm(X, Wo.T) + bo, 0.0)
     out = np.zeros((G, h), f64)
     scale = np.zeros(len(w_atoms), f64)   # d out[g] / d (w-weighted H[a]) incl. w_atoms
     for g, (s, n) in enumerate(a_scope):
@@ -68,8 +82,8 @@ def forward_backward(components, weights, d_out, depth, undirected=False,
         mol_of[s:s + n] = g
     dH = np.where(mol_of[:, None] >= 0, scale[:, None] * d_out[np.maximum(mol_of, 0)], 0.0)
     dZo = dH * (H > 0)
-    grads = {"W_o.weight": dZo.T @ X, "W_o.bias": dZo.sum(0)}
-    dA = dZo @ Wo[:, Fa:]
+    grads = {"W_o.weight": mm(dZo.T, X), "W_o.bias": dZo.sum(0)}
+    dA = mm(dZo, Wo[:, Fa:])
     dM = w_bonds[:, None] * dA[dst]                 # transpose of the final aggregate
     dM[0] = 0.0
     dI = np.zeros_like(I)
@@ -78,9 +92,9 @@ def forward_backward(components, weights, d_out, depth, undirected=False,
     for t in range(depth - 1, 0, -1):
         dZ = dM * (Ms[t] > 0)
         dI += dZ
-        dWh += dZ.T @ Ss[t - 1]
+        dWh += mm(dZ.T, Ss[t - 1])
         dbh += dZ.sum(0)
-        dS = dZ @ Wh
+        dS = mm(dZ, Wh)
         dA = np.zeros((len(w_atoms), h), f64)       # reverse CSR: out-edges of each atom
         for a in range(len(w_atoms)):
             for j in range(out_ptr[a], out_ptr[a + 1]):
@@ -94,7 +108,7 @@ def forward_backward(components, weights, d_out, depth, undirected=False,
         dM = dU
     dZ0 = dM * (I > 0)
     dI += dZ0
-    grads["W_i.weight"] = dI.T @ f_bonds
+    grads["W_i.weight"] = mm(dI.T, f_bonds)
     grads["W_h.weight"] = dWh
     if bi is not None:
         grads["W_i.bias"] = dI.sum(0)

@@ -9,6 +9,8 @@
 //                          (TMA engine) of the pre-swizzled weight chunk for the same stage
 // K is walked in chunks of 32 tf32 (one 128-byte swizzle row); each chunk is 4 MMAs of K=8.
 #pragma once
+#include <cstdlib>
+
 #include "operands.cuh"
 #include "tc_ptx.cuh"
 
@@ -33,9 +35,17 @@ struct TcBarriers {
 
 // N-tiling of an output dimension so that one tile's accumulator fits TMEM and its B stage smem.
 struct TcTiling { int BN, n_tiles; };
+inline int tc_max_bn() {   // WD_TC_MAX_BN: tuning knob (multiple of 16 in [16, 304])
+  static int v = [] {
+    const char* e = getenv("WD_TC_MAX_BN");
+    int x = e ? atoi(e) : TC_MAX_BN;
+    return (x >= 16 && x <= TC_MAX_BN && x % 16 == 0) ? x : TC_MAX_BN;
+  }();
+  return v;
+}
 inline TcTiling tc_tiling(int N) {
   int np = (int)round_up(N, 16);
-  int nt = (int)ceil_div(np, TC_MAX_BN);
+  int nt = (int)ceil_div(np, tc_max_bn());
   int bn = (int)round_up(ceil_div(np, nt), 16);
   return {bn, nt};
 }
@@ -145,6 +155,18 @@ __device__ __forceinline__ void tc_epilogue(uint32_t tmem_acc, int we, int lane,
                                             int64_t row0, int64_t M, int col0, int N, int cmax,
                                             const float* bias, const float* R, int ldr, float* C, int ldc) {
   for (int c0 = 0; c0 < BN; c0 += 32) {
+    const int col = col0 + c0 + lane;
+    const bool in_n = col < N && c0 + lane < BN, in_c = col < cmax && c0 + lane < BN;
+    // residual rows first: 32 independent coalesced loads in flight while TMEM is read
+    float rv[32];
+    if (EPI == E_RES_ACT) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const int64_t r = row0 + we * 32 + i;
+        rv[i] = (in_n && r < M) ? __ldg(R + r * ldr + col) : 0.f;
+      }
+    }
+    const float bv = (bias != nullptr && in_n) ? __ldg(bias + col) : 0.f;
     float v[32];
     const uint32_t ta = tmem_acc + ((uint32_t)(we * 32) << 16) + (uint32_t)c0;
     if (BN - c0 >= 32) {
@@ -158,17 +180,13 @@ __device__ __forceinline__ void tc_epilogue(uint32_t tmem_acc, int we, int lane,
 #pragma unroll
     for (int j = 0; j < 32; ++j) st[lane * 33 + j] = v[j];
     __syncwarp();
-    const int col = col0 + c0 + lane;
-    const bool in_n = col < N && c0 + lane < BN, in_c = col < cmax && c0 + lane < BN;
-    const float bv = (bias != nullptr && in_n) ? __ldg(bias + col) : 0.f;
-#pragma unroll 8
+#pragma unroll
     for (int i = 0; i < 32; ++i) {
       const int64_t r = row0 + we * 32 + i;
-      if (r >= M || !in_c) continue;
       float x = st[i * 33 + lane] + bv;
-      if (EPI == E_RES_ACT && in_n) x += __ldg(R + r * ldr + col);
+      if (EPI == E_RES_ACT) x += rv[i];
       if (EPI != E_STORE) x = act_fwd<ACT>(x);
-      C[r * ldc + col] = in_n ? x : 0.f;
+      if (r < M && in_c) C[r * ldc + col] = in_n ? x : 0.f;
     }
     __syncwarp();
   }
