@@ -26,6 +26,8 @@ struct Layout {
   float* p(void* ws, int64_t off) const { return reinterpret_cast<float*>(ws) + off; }
 };
 
+constexpr int kColsumMaxChunks = 512;   // row chunks of the bias-gradient column sums
+
 int dw_chunks(int64_t rows, int n1, int n2) {
   int64_t tiles = ceil_div(n1, DW_BM) * ceil_div(n2, DW_BN);
   int64_t z = ceil_div(4 * kNumSMs, tiles);
@@ -65,7 +67,7 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   L.Z = std::max(std::max(L.Zh, L.Zi), L.Zo);
   int64_t pw = std::max<int64_t>((int64_t)std::max(1, c.depth - 1) * h * h,
                                  (int64_t)h * std::max(Fo, c.bond_fdim));
-  L.partials = take((int64_t)L.Z * pw + (int64_t)L.Z * h);
+  L.partials = take((int64_t)L.Z * pw + (int64_t)kColsumMaxChunks * h);
   L.pWi = tc_packed_geometry(h, c.bond_fdim, 0);     // I = f_bonds W_i^T
   L.pWh = tc_packed_geometry(h, h, 0);               // S W_h^T
   L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
@@ -141,7 +143,9 @@ int reduce_partials(cudaStream_t s, const float* P, float* out, int64_t n, int Z
   return WD_OK;
 }
 
-int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_t R, int N, int Z) {
+// bias gradients: column sums over many short row chunks (coalesced row reads), then a fixed-order reduction
+int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_t R, int N, int /*Zdw*/) {
+  const int Z = (int)std::max<int64_t>(1, std::min<int64_t>(kColsumMaxChunks, R / 64));
   int64_t rpc = ceil_div(R, Z);
   WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc);
   return reduce_partials(s, P, out, N, Z);

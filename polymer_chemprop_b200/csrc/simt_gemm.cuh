@@ -177,9 +177,14 @@ __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   int64_t r_begin = (int64_t)blockIdx.y * rows_per_chunk, r_end = min(R, r_begin + rows_per_chunk);
-  float s = 0.f;
-  for (int64_t r = r_begin; r < r_end; ++r) s += __ldg(X + r * ldx + n);
-  P[(int64_t)blockIdx.y * N + n] = s;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;    // fixed association order: deterministic
+  int64_t r = r_begin;
+  for (; r + 4 <= r_end; r += 4) {
+    s0 += __ldg(X + (r + 0) * ldx + n); s1 += __ldg(X + (r + 1) * ldx + n);
+    s2 += __ldg(X + (r + 2) * ldx + n); s3 += __ldg(X + (r + 3) * ldx + n);
+  }
+  for (; r < r_end; ++r) s0 += __ldg(X + r * ldx + n);
+  P[(int64_t)blockIdx.y * N + n] = (s0 + s1) + (s2 + s3);
 }
 
 // out[i] = sum_z P[z][i] in ascending z (fixed order => bitwise reproducible)

@@ -12,7 +12,7 @@
 
 namespace wd {
 
-constexpr int TC_DW_MAX_TILES = 12;
+constexpr int TC_DW_MAX_TILES = 24;
 
 struct TcDwTile {
   int seg;       // 0: Y.X (or the gathered operand), 1: Y.X2 (second CONCAT segment)

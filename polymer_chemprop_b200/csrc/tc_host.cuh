@@ -1,6 +1,8 @@
 // Host-side launch helpers of the tcgen05 contraction kernels (tc_gemm.cuh / tc_dw.cuh).
 #pragma once
 #include "tc_dw.cuh"
+#include "tc_dw2.cuh"
+#include "tc_gemm2.cuh"
 
 namespace wd {
 
@@ -11,8 +13,18 @@ struct TcPacked {
   int64_t floats() const { return (int64_t)n_tiles * KC * BN * 32; }
 };
 
+inline bool tc_use_v1() {   // WD_TC_V1=1: first-generation (register-staged) kernels, for A/B comparisons
+  static bool v = [] { const char* e = getenv("WD_TC_V1"); return e && atoi(e) != 0; }();
+  return v;
+}
+
 inline TcPacked tc_packed_geometry(int N, int K1, int K2) {
   TcTiling t = tc_tiling(N);
+  if (!tc_use_v1() && t.BN > T2_MAX_BN) {     // second generation: two accumulators must fit TMEM
+    const int np = (int)round_up(N, 16);
+    t.n_tiles = (int)ceil_div(np, std::min(tc_max_bn(), T2_MAX_BN));
+    t.BN = (int)round_up(ceil_div(np, t.n_tiles), 16);
+  }
   TcPacked g{N, K1, K2, t.BN, t.n_tiles, (int)ceil_div(K1, TC_BK), 0, nullptr};
   g.KC = g.KC1 + (int)ceil_div(K2, TC_BK);
   return g;
@@ -33,10 +45,40 @@ inline int tc_set_smem(Kernel k, int bytes) {
   return WD_OK;
 }
 
+// second-generation kernel (cp.async raw ring + transform warps)
+template <int AMODE, int EPI, int ACT, bool PREACT>
+int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
+             float* C, int ldc, int64_t M) {
+  T2Params p{};
+  constexpr int NSRC = AMODE == A_GATHER_DIFF ? 2 : 1;
+  if (AMODE == A_GATHER_DIFF) {
+    p.seg[0] = T2Seg{A.X, A.X2, A.src, A.rev, A.ldx, A.ldx2, B.K1, 1};
+    if (!tc_aligned16(A.X, A.ldx) || !tc_aligned16(A.X2, A.ldx2))
+      return fail(WD_ERR_INVALID_ARG, "tcgen05 gather operand needs 16-byte aligned rows");
+  } else {
+    p.seg[0] = T2Seg{A.X, nullptr, nullptr, nullptr, A.ldx, 0, B.K1, tc_aligned16(A.X, A.ldx) ? 1 : 0};
+    if (AMODE == A_CONCAT) p.seg[1] = T2Seg{A.X2, nullptr, nullptr, nullptr, A.ldx2, 0, B.K2, tc_aligned16(A.X2, A.ldx2) ? 1 : 0};
+  }
+  p.KC0 = B.KC1; p.KC = B.KC;
+  p.Bp = B.img; p.bias = bias; p.R = R; p.ldr = ldr; p.C = C; p.ldc = ldc; p.M = M;
+  p.N = B.N; p.BN = B.BN; p.n_tiles = B.n_tiles;
+  const int smem = t2_smem_bytes(B.BN);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 tile does not fit shared memory");
+  if (EPI == E_RES_ACT && (!tc_aligned16(R, ldr))) return fail(WD_ERR_INVALID_ARG, "tcgen05 residual rows must be 16-byte aligned");
+  auto kern = k_tc_gemm2<NSRC, EPI, ACT, PREACT>;
+  int rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  const int64_t tiles = ceil_div(M, TC_BM) * B.n_tiles;
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
+  WD_LAUNCH(kern, grid, T2_THREADS, smem, s, p);
+  return WD_OK;
+}
+
 // C[M, ldc] = epi( A[M, K1+K2] * B^T ) with B packed
 template <int AMODE, int EPI, int ACT, bool PREACT>
 int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
             float* C, int ldc, int64_t M) {
+  if (!tc_use_v1()) return tc_gemm2<AMODE, EPI, ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M);
   TcGemmParams p{};
   p.A = A;
   p.A.K1 = B.K1;
@@ -61,13 +103,16 @@ int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* b
 
 // n2 tiles of a dW contraction: each segment split into tiles of <= TC_MAX_BN columns
 inline int tc_dw_tiles(int w0, int w1, TcDwTile* out) {
+  const int max_bn = tc_use_v1() ? tc_max_bn() : std::min(tc_max_bn(), D2_MAX_BN);
   int n = 0;
   const int widths[2] = {w0, w1};
   int out0 = 0;
   for (int seg = 0; seg < 2; ++seg) {
     const int w = widths[seg];
     if (w <= 0) continue;
-    TcTiling t = tc_tiling(w);
+    TcTiling t;
+    t.n_tiles = (int)ceil_div(round_up(w, 16), max_bn);
+    t.BN = (int)round_up(ceil_div(round_up(w, 16), t.n_tiles), 16);
     for (int j = 0; j < t.n_tiles; ++j) {
       const int col0 = j * t.BN;
       const int width = std::min(t.BN, w - col0);
@@ -95,10 +140,46 @@ inline int tc_dw_z(int64_t rows, int n1, int n2_tiles) {
   return (int)ceil_div(rows, rpz);
 }
 
+// second-generation dW kernel (raw row ring + transposing transform warps)
+template <int YMODE, int ACT, bool PREACT>
+int tc_dw2(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
+           int Z) {
+  constexpr int NSRC = YMODE == A_GATHER_DIFF ? 2 : 1;
+  D2Params p{};
+  if (!tc_aligned16(X, ldx)) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: X rows must be 16-byte aligned");
+  p.X = X; p.ldx = ldx; p.N1 = N1; p.P = P; p.ldp = w0 + w1; p.R = R;
+  p.Y0[0] = Y.X; p.ldy[0] = Y.ldx; p.align16[0] = tc_aligned16(Y.X, Y.ldx) ? 1 : 0;
+  if (YMODE == A_GATHER_DIFF) {
+    p.Y1 = Y.X2; p.ldy1 = Y.ldx2; p.i0 = Y.src; p.i1 = Y.rev;
+    if (!p.align16[0] || !tc_aligned16(Y.X2, Y.ldx2))
+      return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: gather operand needs 16-byte aligned rows");
+  } else if (YMODE == A_CONCAT) {
+    p.Y0[1] = Y.X2; p.ldy[1] = Y.ldx2; p.align16[1] = tc_aligned16(Y.X2, Y.ldx2) ? 1 : 0;
+  }
+  p.n2_tiles = tc_dw_tiles(w0, w1, p.t);
+  if (p.n2_tiles <= 0) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW: too many column tiles");
+  p.n1_tiles = (int)ceil_div(N1, TC_BM);
+  p.rows_per_z = round_up(ceil_div(R, Z), TC_BK);
+  if (ceil_div(R, p.rows_per_z) != Z) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: inconsistent row chunking");
+  p.maxBN = 16;
+  for (int i = 0; i < p.n2_tiles; ++i) p.maxBN = std::max(p.maxBN, p.t[i].BN);
+  p.raw_stages = D2_MAX_RAW_STAGES;
+  while (p.raw_stages > 1 && d2_smem_bytes(p.maxBN, NSRC, p.raw_stages) > TC_SMEM_LIMIT) --p.raw_stages;
+  const int smem = d2_smem_bytes(p.maxBN, NSRC, p.raw_stages);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW tile does not fit shared memory");
+  auto kern = k_tc_dw2<NSRC, ACT, PREACT>;
+  int rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  dim3 grid((unsigned)(p.n1_tiles * p.n2_tiles), (unsigned)Z);
+  WD_LAUNCH(kern, grid, T2_THREADS, smem, s, p);
+  return WD_OK;
+}
+
 // P[0..Z) <- partial X^T Y over Z row chunks (Z from tc_dw_z)
 template <int YMODE, int ACT, bool PREACT>
 int tc_dw(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
           int Z) {
+  if (!tc_use_v1()) return tc_dw2<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
   TcDwParams p{};
   p.X = X; p.ldx = ldx; p.N1 = N1; p.Y = Y; p.P = P; p.ldp = w0 + w1; p.R = R;
   p.n2_tiles = tc_dw_tiles(w0, w1, p.t);
