@@ -149,8 +149,9 @@ enum {
   WD_PROF_DW = 6,          /* weight-gradient contractions dW_h / dW_i / dW_o / biases           */
   WD_PROF_DX = 7,          /* dS = dZ W_h and dA_d = dZo W_o[:, F_a:]                            */
   WD_PROF_SCATTER = 8,     /* transpose-CSR scatter of dS onto source atoms                      */
-  WD_PROF_MISC = 9,        /* CSR build, symmetrisation, everything else                         */
-  WD_PROF_NUM = 10
+  WD_PROF_MISC = 9,        /* CSR build, symmetrisation, weight packing, everything else         */
+  WD_PROF_REDUCE = 10,     /* fixed-order reduction of split-K partials, bias-gradient column sums */
+  WD_PROF_NUM = 11
 };
 void wd_profile_enable(int on); /* on != 0: record events around every launch from now on      */
 void wd_profile_reset(void);    /* forget recorded launches (keeps the event pool)              */
@@ -162,7 +163,7 @@ int wd_profile_read(int category, double* total_ms, int64_t* launches);
  * wd_debug_gemm: C[M, ldc] = epi(A[M,K] * B^T + bias (+ R)); B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k];
  *   epi 0 = store, 1 = ReLU, 2 = ReLU(R + .).  Columns [N, ldc) of C are zero-filled.
  *   TF32 mode needs `scratch` >= 4 * round_up(N,304-ish tiles) * round_up(K,32) bytes (packed weights).
- * wd_debug_dw: out[N1, N2] = X[R, :N1]^T * Y[R, :N2]; `scratch` >= 64 * N1 * N2 * 4 bytes (partials). */
+ * wd_debug_dw: out[N1, N2] = X[R, :N1]^T * Y[R, :N2]; `scratch` >= 160 * N1 * N2 * 4 bytes (partials). */
 int wd_debug_gemm(const float* A, int lda, const float* W, int ldb, int b_kn, const float* bias,
                   const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, int epi,
                   int math_mode, void* scratch, size_t scratch_bytes, void* stream);

@@ -9,7 +9,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwdmpnn.so")
+LIB_PATH = os.environ.get("WDMPNN_LIB") or os.path.join(_HERE, "libwdmpnn.so")
 
 WD_OK, WD_ERR_INVALID_ARG, WD_ERR_CUDA, WD_ERR_UNSUPPORTED, WD_ERR_GRAPH = 0, -1, -2, -3, -4
 ACTIVATIONS = {"ReLU": 0, "LeakyReLU": 1, "tanh": 2, "SELU": 3, "ELU": 4}
@@ -48,7 +48,7 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_workspace_bytes", "wd_encod
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
            "wd_debug_dw")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
-                   "dx", "scatter", "misc")
+                   "dx", "scatter", "misc", "reduce")
 
 _lib = None
 

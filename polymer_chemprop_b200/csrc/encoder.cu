@@ -38,7 +38,7 @@ int dw_chunks(int64_t rows, int n1, int n2) {
 Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   Layout L;
   const int h = c.hidden_size;
-  L.ldh = (int)round_up(h, 4);
+  L.ldh = (int)round_up(h, 8);   // rows start on 32-byte sectors: a 128-byte row chunk is exactly 4 sectors
   L.szB = round_up(Nb * L.ldh, 64);
   L.szA = round_up(Na * L.ldh, 64);
   int64_t off = 0;
@@ -139,12 +139,14 @@ int bind_packed(const WdConfig& c, Layout& L, void* ws) {
 }
 
 int reduce_partials(cudaStream_t s, const float* P, float* out, int64_t n, int Z) {
+  ProfScope ps(WD_PROF_REDUCE);
   WD_LAUNCH(k_reduce_partials, grid1d(n), 256, 0, s, P, out, n, Z);
   return WD_OK;
 }
 
 // bias gradients: column sums over many short row chunks (coalesced row reads), then a fixed-order reduction
 int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_t R, int N, int /*Zdw*/) {
+  ProfScope ps(WD_PROF_REDUCE);
   const int Z = (int)std::max<int64_t>(1, std::min<int64_t>(kColsumMaxChunks, R / 64));
   int64_t rpc = ceil_div(R, Z);
   WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc);

@@ -13,6 +13,15 @@ namespace wd {
 constexpr int D2_MAX_BN = 160;                       // Y columns per CTA
 constexpr int D2_X_RAW = TC_BK * TC_BM * 4;          // 16 KB: 32 rows x 128 columns
 constexpr int D2_OP_STAGES = 2, D2_MAX_RAW_STAGES = 3;
+// warp roles: 0-3 epilogue, 4 MMA, 5 idle, 6.. loaders, then transform warps (8: the transposing
+// transform is the instruction-heaviest role; measured 0.248 -> 0.200 ms per launch going from 4 to 8)
+#ifndef WD_D2_XFORM_WARPS
+#define WD_D2_XFORM_WARPS 8
+#endif
+constexpr int D2_LOAD_WARPS = 4, D2_XFORM_WARPS = WD_D2_XFORM_WARPS;
+constexpr int D2_LOAD_T0 = 32 * 6, D2_LOAD_THREADS = 32 * D2_LOAD_WARPS;
+constexpr int D2_XFORM_W0 = 6 + D2_LOAD_WARPS;
+constexpr int D2_THREADS = 32 * (D2_XFORM_W0 + D2_XFORM_WARPS);
 
 struct D2Barriers {
   uint64_t raw_full[D2_MAX_RAW_STAGES], raw_empty[D2_MAX_RAW_STAGES], op_full[D2_OP_STAGES], op_empty[D2_OP_STAGES];
@@ -43,7 +52,7 @@ inline int d2_smem_bytes(int maxBN, int nsrc, int raw_stages) {
 }
 
 template <int NSRC, int ACT, bool PREACT>
-__global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
+__global__ void __launch_bounds__(D2_THREADS, 1) k_tc_dw2(const D2Params p) {
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);
@@ -57,8 +66,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
   D2Barriers* bar = reinterpret_cast<D2Barriers*>(raw + SR * raw_stage + TC_EPI_STAGE_BYTES);
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < SR; ++s) { ptx::mbar_init(&bar->raw_full[s], T2_LOAD_THREADS); ptx::mbar_init(&bar->raw_empty[s], T2_XFORM_WARPS); }
-    for (int s = 0; s < D2_OP_STAGES; ++s) { ptx::mbar_init(&bar->op_full[s], T2_XFORM_WARPS); ptx::mbar_init(&bar->op_empty[s], 1); }
+    for (int s = 0; s < SR; ++s) { ptx::mbar_init(&bar->raw_full[s], D2_LOAD_THREADS); ptx::mbar_init(&bar->raw_empty[s], D2_XFORM_WARPS); }
+    for (int s = 0; s < D2_OP_STAGES; ++s) { ptx::mbar_init(&bar->op_full[s], D2_XFORM_WARPS); ptx::mbar_init(&bar->op_empty[s], 1); }
     ptx::mbar_init(&bar->tmem_full, 1);
     ptx::fence_barrier_init();
   }
@@ -75,9 +84,9 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
   const int KC = (int)ceil_div(r_end - r_begin, TC_BK);        // host guarantees >= 1
   const int ystride = p.maxBN * 4;                             // raw Y row stride in bytes
 
-  if (warp >= 6 + T2_LOAD_WARPS && warp < T2_RLOAD_WARP) {
+  if (warp >= D2_XFORM_W0) {
     // ================= transform: transpose raw rows into K-major swizzled operand stages =================
-    const int tw = warp - 6 - T2_LOAD_WARPS;
+    const int tw = warp - D2_XFORM_W0;
     const int ygroups = (int)ceil_div(tl.BN, 32);
     for (int kc = 0; kc < KC; ++kc) {
       const int s = kc % SR, os = kc % D2_OP_STAGES;
@@ -88,7 +97,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
       uint8_t* oa = opA + os * op_stage;
       uint8_t* ob = oa + TC_A_STAGE;
       // X: 4 column groups x 8 row quads
-      for (int q = tw; q < 32; q += T2_XFORM_WARPS) {
+      for (int q = tw; q < 32; q += D2_XFORM_WARPS) {
         const int m = (q >> 3) * 32 + lane, kq = q & 7;
         float x[4];
 #pragma unroll
@@ -96,7 +105,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
         tc_store_piece(oa, m, kq, make_float4(x[0], x[1], x[2], x[3]));
       }
       // Y: ygroups column groups x 8 row quads
-      for (int q = tw; q < ygroups * 8; q += T2_XFORM_WARPS) {
+      for (int q = tw; q < ygroups * 8; q += D2_XFORM_WARPS) {
         const int n = (q >> 3) * 32 + lane, kq = q & 7;
         if (n < tl.BN) {
           float y[4];
@@ -118,9 +127,10 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
       __syncwarp();
       if (lane == 0) { ptx::mbar_arrive(&bar->op_full[os]); ptx::mbar_arrive(&bar->raw_empty[s]); }
     }
-  } else if (warp >= 6 && warp < 6 + T2_LOAD_WARPS) {
-    // ================= loaders: thread owns one of the stage's 32 rows (4 threads per row) =================
-    const int t = threadIdx.x - T2_LOAD_T0, rl = t >> 2, q4 = t & 3;
+  } else if (warp >= 6) {
+    // ================= loaders: thread owns one of the stage's 32 rows (LPR threads per row) =================
+    constexpr int LPR = D2_LOAD_THREADS / TC_BK;               // loader threads per row
+    const int t = threadIdx.x - D2_LOAD_T0, rl = t / LPR, q4 = t % LPR;
     const uint32_t raw_u32 = ptx::smem_u32(raw);
     const int seg = tl.seg;
     const float* Y0 = p.Y0[seg];
@@ -139,8 +149,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
       // X: 32 pieces of 16 bytes per row
       const float* xrow = p.X + (ok ? r : 0) * p.ldx + n1_0;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int c = q4 + 4 * i;
+      for (int i = 0; i < 32 / LPR; ++i) {
+        const int c = q4 + LPR * i;
         const int rem = (p.N1 - (n1_0 + c * 4)) * 4;
         const uint32_t v = !ok ? 0u : (rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u));
         ptx::cp_async16(dx + c * 16, v ? xrow + c * 4 : p.X, v);
@@ -148,14 +158,14 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_dw2(const D2Params p) {
       // Y: BN/4 pieces per row and source
       const float* y0row = Y0 + ra * ldy + tl.col0;
       if (al) {
-        for (int c = q4; c < tl.BN / 4; c += 4) {
+        for (int c = q4; c < tl.BN / 4; c += LPR) {
           const int rem = (tl.width - c * 4) * 4;
           const uint32_t v = !ok ? 0u : (rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u));
           ptx::cp_async16(dy + c * 16, v ? y0row + c * 4 : Y0, v);
           if (NSRC == 2) ptx::cp_async16(dy + y_raw + c * 16, v ? p.Y1 + rb * p.ldy1 + tl.col0 + c * 4 : p.Y1, v);
         }
       } else {
-        for (int c = q4; c < tl.BN; c += 4) {
+        for (int c = q4; c < tl.BN; c += LPR) {
           const uint32_t v = (ok && c < tl.width) ? 4u : 0u;
           ptx::cp_async4(dy + c * 4, v ? y0row + c : Y0, v);
         }

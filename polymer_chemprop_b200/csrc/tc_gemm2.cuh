@@ -16,7 +16,14 @@
 
 namespace wd {
 
-constexpr int T2_EPI_WARPS = 4, T2_MMA_WARP = 4, T2_BLOAD_WARP = 5, T2_LOAD_WARPS = 4, T2_XFORM_WARPS = 4;
+#ifndef WD_T2_LOAD_WARPS
+#define WD_T2_LOAD_WARPS 4
+#endif
+#ifndef WD_T2_XFORM_WARPS
+#define WD_T2_XFORM_WARPS 4
+#endif
+constexpr int T2_EPI_WARPS = 4, T2_MMA_WARP = 4, T2_BLOAD_WARP = 5, T2_LOAD_WARPS = WD_T2_LOAD_WARPS,
+              T2_XFORM_WARPS = WD_T2_XFORM_WARPS;
 constexpr int T2_LOAD_T0 = 32 * 6, T2_XFORM_T0 = 32 * (6 + T2_LOAD_WARPS);
 constexpr int T2_RLOAD_WARP = 6 + T2_LOAD_WARPS + T2_XFORM_WARPS;   // residual loader (one warp)
 constexpr int T2_THREADS = 32 * (T2_RLOAD_WARP + 1);
@@ -25,6 +32,8 @@ constexpr int T2_R_SLOTS = 3, T2_R_ROW = 144;     // residual / staging ring: 12
 constexpr int T2_R_SLOT_BYTES = TC_BM * T2_R_ROW;
 constexpr int T2_R_BYTES = T2_R_SLOTS * T2_R_SLOT_BYTES;
 constexpr int T2_LOAD_THREADS = 32 * T2_LOAD_WARPS, T2_XFORM_THREADS = 32 * T2_XFORM_WARPS;
+constexpr int T2_LR = T2_LOAD_THREADS / 8, T2_LJ = TC_BM / T2_LR;      // loader: rows per pass / passes per 128-row chunk
+constexpr int T2_XR = T2_XFORM_THREADS / 8, T2_XJ = TC_BM / T2_XR;     // transform: same
 constexpr int T2_RAW_SLOTS = 6;                   // raw ring: 6 x 16 KB (3 stages of 2 sources or 6 of 1)
 constexpr int T2_RAW_BYTES = T2_RAW_SLOTS * TC_A_STAGE;
 constexpr int T2_OP_STAGES = 2;                   // operand rings (A swizzled, B weights)
@@ -171,7 +180,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
     }
   } else if (warp >= 6 + T2_LOAD_WARPS) {
     // ================= transform: raw ring -> swizzled TF32 operand ring =================
-    const int t = threadIdx.x - T2_XFORM_T0, c = t & 7, rb = t >> 3;     // rows rb + 16 j
+    const int t = threadIdx.x - T2_XFORM_T0, c = t & 7, rb = t >> 3;     // rows rb + T2_XR * j
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
       for (int kc = 0; kc < p.KC; ++kc, ++it) {
@@ -181,8 +190,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
         const uint8_t* rs = raw + s * RAW_STAGE;
         uint8_t* oa = opA + as * TC_A_STAGE;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int rl = rb + 16 * j;
+        for (int j = 0; j < T2_XJ; ++j) {
+          const int rl = rb + T2_XR * j;
           float4 v = *reinterpret_cast<const float4*>(rs + rl * 128 + c * 16);
           if (NSRC == 2) {
             float4 u = *reinterpret_cast<const float4*>(rs + TC_A_STAGE + rl * 128 + c * 16);
@@ -203,13 +212,13 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
       const int64_t row0 = (tile / p.n_tiles) * TC_BM;
-      // 16-byte path: thread owns chunk column c of rows rb + 16 j
+      // 16-byte path: thread owns chunk column c of rows rb + T2_LR * j
       const int c = t & 7, rb = t >> 3;
-      int64_t o0[8], o1[8];
+      int64_t o0[T2_LJ], o1[T2_LJ];
       uint32_t okmask = 0;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int64_t r = row0 + rb + 16 * j;
+      for (int j = 0; j < T2_LJ; ++j) {
+        const int64_t r = row0 + rb + T2_LR * j;
         const bool ok = r < p.M;
         okmask |= (ok ? 1u : 0u) << j;
         int64_t a = ok ? r : 0, b = a;
@@ -230,10 +239,10 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
           const int rem = (sg.K - k) * 4;
           const uint32_t valid = rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < T2_LJ; ++j) {
             const uint32_t v = ((okmask >> j) & 1u) ? valid : 0u;
-            const int64_t ra = second ? row0 + rb + 16 * j : o0[j];
-            const uint32_t d = dst + (rb + 16 * j) * 128 + c * 16;
+            const int64_t ra = second ? row0 + rb + T2_LR * j : o0[j];
+            const uint32_t d = dst + (rb + T2_LR * j) * 128 + c * 16;
             ptx::cp_async16(d, v ? sg.X0 + ra * sg.ld0 + k : sg.X0, v);
             if (NSRC == 2) ptx::cp_async16(d + TC_A_STAGE, v ? sg.X1 + o1[j] * sg.ld1 + k : sg.X1, v);
           }
@@ -241,8 +250,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
           const int col = t & 31, r4 = t >> 5, k = kbase + col;
           const bool vk = k < sg.K;
 #pragma unroll 8
-          for (int j = 0; j < 32; ++j) {
-            const int rl = r4 + 4 * j;
+          for (int j = 0; j < TC_BM / T2_LOAD_WARPS; ++j) {
+            const int rl = r4 + T2_LOAD_WARPS * j;
             const int64_t r = row0 + rl;
             const uint32_t v = (vk && r < p.M) ? 4u : 0u;
             ptx::cp_async4(dst + rl * 128 + col * 4, v ? sg.X0 + r * sg.ld0 + k : sg.X0, v);

@@ -2,6 +2,7 @@
 #pragma once
 #include "tc_dw.cuh"
 #include "tc_dw2.cuh"
+#include "tc_dw3.cuh"
 #include "tc_gemm2.cuh"
 
 namespace wd {
@@ -16,6 +17,11 @@ struct TcPacked {
 inline bool tc_use_v1() {   // WD_TC_V1=1: first-generation (register-staged) kernels, for A/B comparisons
   static bool v = [] { const char* e = getenv("WD_TC_V1"); return e && atoi(e) != 0; }();
   return v;
+}
+
+inline int tc_dw_version() {   // WD_TC_DW=1|2|3: generation of the dW kernel (default 3), for A/B comparisons
+  static int v = [] { const char* e = getenv("WD_TC_DW"); int x = e ? atoi(e) : 3; return (x >= 1 && x <= 3) ? x : 3; }();
+  return tc_use_v1() ? 1 : v;
 }
 
 inline TcPacked tc_packed_geometry(int N, int K1, int K2) {
@@ -103,7 +109,7 @@ int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* b
 
 // n2 tiles of a dW contraction: each segment split into tiles of <= TC_MAX_BN columns
 inline int tc_dw_tiles(int w0, int w1, TcDwTile* out) {
-  const int max_bn = tc_use_v1() ? tc_max_bn() : std::min(tc_max_bn(), D2_MAX_BN);
+  const int max_bn = tc_dw_version() == 1 ? tc_max_bn() : std::min(tc_max_bn(), D2_MAX_BN);
   int n = 0;
   const int widths[2] = {w0, w1};
   int out0 = 0;
@@ -132,10 +138,10 @@ inline int tc_dw_count_tiles(int w0, int w1) {
 
 // number of row chunks so that the grid roughly fills the GPU once
 inline int tc_dw_z(int64_t rows, int n1, int n2_tiles) {
-  const int64_t ctas = ceil_div(n1, TC_BM) * std::max(1, n2_tiles);
+  const int64_t ctas = ceil_div(n1, tc_dw_version() == 3 ? D3_MROWS : TC_BM) * std::max(1, n2_tiles);
   int64_t z = std::max<int64_t>(1, kNumSMs / ctas);
   z = std::min<int64_t>(z, std::max<int64_t>(1, rows / 128));
-  z = std::min<int64_t>(z, 64);
+  z = std::min<int64_t>(z, kNumSMs);
   const int64_t rpz = round_up(ceil_div(rows, z), TC_BK);
   return (int)ceil_div(rows, rpz);
 }
@@ -171,7 +177,43 @@ int tc_dw2(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, i
   int rc = tc_set_smem(kern, smem);
   if (rc != WD_OK) return rc;
   dim3 grid((unsigned)(p.n1_tiles * p.n2_tiles), (unsigned)Z);
-  WD_LAUNCH(kern, grid, T2_THREADS, smem, s, p);
+  WD_LAUNCH(kern, grid, D2_THREADS, smem, s, p);
+  return WD_OK;
+}
+
+// third-generation dW kernel (up to 384 X columns per CTA, 16-row chunks, SWIZZLE_64B operand stages)
+template <int YMODE, int ACT, bool PREACT>
+int tc_dw3(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
+           int Z) {
+  constexpr int NSRC = YMODE == A_GATHER_DIFF ? 2 : 1;
+  D3Params p{};
+  if (!tc_aligned16(X, ldx)) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: X rows must be 16-byte aligned");
+  p.X = X; p.ldx = ldx; p.N1 = N1; p.P = P; p.ldp = w0 + w1; p.R = R;
+  p.Y0[0] = Y.X; p.ldy[0] = Y.ldx; p.align16[0] = tc_aligned16(Y.X, Y.ldx) ? 1 : 0;
+  if (YMODE == A_GATHER_DIFF) {
+    p.Y1 = Y.X2; p.ldy1 = Y.ldx2; p.i0 = Y.src; p.i1 = Y.rev;
+    if (!p.align16[0] || !tc_aligned16(Y.X2, Y.ldx2))
+      return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: gather operand needs 16-byte aligned rows");
+  } else if (YMODE == A_CONCAT) {
+    p.Y0[1] = Y.X2; p.ldy[1] = Y.ldx2; p.align16[1] = tc_aligned16(Y.X2, Y.ldx2) ? 1 : 0;
+  }
+  p.n2_tiles = tc_dw_tiles(w0, w1, p.t);
+  if (p.n2_tiles <= 0) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW: too many column tiles");
+  p.n1_groups = (int)ceil_div(N1, D3_MROWS);
+  p.xw = (int)round_up(std::min(N1, D3_MROWS), 32);
+  p.rows_per_z = round_up(ceil_div(R, Z), TC_BK);
+  if (ceil_div(R, p.rows_per_z) != Z) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: inconsistent row chunking");
+  p.maxBN = 16;
+  for (int i = 0; i < p.n2_tiles; ++i) p.maxBN = std::max(p.maxBN, p.t[i].BN);
+  p.raw_stages = D3_MAX_RAW_STAGES;
+  while (p.raw_stages > 1 && d3_smem_bytes(p.xw, p.maxBN, NSRC, p.raw_stages) > TC_SMEM_LIMIT) --p.raw_stages;
+  const int smem = d3_smem_bytes(p.xw, p.maxBN, NSRC, p.raw_stages);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW tile does not fit shared memory");
+  auto kern = k_tc_dw3<NSRC, ACT, PREACT>;
+  int rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  dim3 grid((unsigned)(p.n1_groups * p.n2_tiles), (unsigned)Z);
+  WD_LAUNCH(kern, grid, D3_THREADS, smem, s, p);
   return WD_OK;
 }
 
@@ -179,7 +221,8 @@ int tc_dw2(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, i
 template <int YMODE, int ACT, bool PREACT>
 int tc_dw(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
           int Z) {
-  if (!tc_use_v1()) return tc_dw2<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
+  if (tc_dw_version() == 3) return tc_dw3<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
+  if (tc_dw_version() == 2) return tc_dw2<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
   TcDwParams p{};
   p.X = X; p.ldx = ldx; p.N1 = N1; p.Y = Y; p.P = P; p.ldp = w0 + w1; p.R = R;
   p.n2_tiles = tc_dw_tiles(w0, w1, p.t);

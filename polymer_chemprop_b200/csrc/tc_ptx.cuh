@@ -26,8 +26,20 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+#ifndef WD_WAIT_HINT_NS
+#define WD_WAIT_HINT_NS 0     // > 0: suspend-time hint of mbarrier.try_wait (parks the warp instead of polling)
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
+#if WD_WAIT_HINT_NS > 0
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"((uint32_t)WD_WAIT_HINT_NS)
+      : "memory");
+#else
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -35,12 +47,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
+#endif
   return ok != 0;
 }
 // Bounded spin: a protocol bug traps (-> cudaErrorLaunchFailure) instead of hanging the GPU.
+#ifndef WD_WAIT_SLEEP_NS
+#define WD_WAIT_SLEEP_NS 0    // > 0: back off with __nanosleep between polls
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+#if WD_WAIT_SLEEP_NS > 0
+    __nanosleep(WD_WAIT_SLEEP_NS);
+#endif
     if (++spins > (1u << 22)) __trap();
   }
 }

@@ -82,7 +82,7 @@ def probe_dw(Rn, N1, N2):
     res = {}
     for mode, name in ((0, "fp32"), (1, "tf32")):
         out = torch.full((N1, N2), float("nan"), device=DEV)
-        scratch = torch.empty(64 * N1 * N2 * 4, dtype=torch.uint8, device=DEV)
+        scratch = torch.empty(160 * N1 * N2 * 4, dtype=torch.uint8, device=DEV)
         try:
             _capi.check(L.wd_debug_dw(p(X), ld1, p(Y), ld2, p(out), Rn, N1, N2, mode, p(scratch), scratch.numel(),
                                       _capi.current_stream(DEV)))

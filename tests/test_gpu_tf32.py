@@ -69,7 +69,7 @@ def test_tc_dw_matches_fp64(R, N1, N2):
     X = torch.randn(R, ld1, device=DEV, generator=g)
     Y = torch.randn(R, N2, device=DEV, generator=g)
     out = torch.full((N1, N2), float("nan"), device=DEV)
-    scratch = torch.empty(64 * N1 * N2 * 4, dtype=torch.uint8, device=DEV)
+    scratch = torch.empty(160 * N1 * N2 * 4, dtype=torch.uint8, device=DEV)
     _capi.check(L.wd_debug_dw(p(X), ld1, p(Y), N2, p(out), R, N1, N2, 1, p(scratch), scratch.numel(),
                               _capi.current_stream(DEV)))
     torch.cuda.synchronize()
