@@ -247,15 +247,16 @@ def main():
     Na, Nb, G = dg.n_atoms, dg.n_bonds, dg.n_mols
     d_out = torch.randn(G, a.hidden, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
 
+    from polymer_chemprop_b200 import dp
+    reducer = dp.FlatGradAllReduce(params) if world > 1 else None
+
     def step():
         for p in params:
             p.grad = None
         out = model([bmg])
         out.backward(d_out)
         if world > 1:                                    # data-parallel gradient all-reduce (one flat buffer)
-            flat = torch.cat([p.grad.reshape(-1) for p in params])
-            dist.all_reduce(flat)
-            flat.div_(world)
+            reducer()
         return out
 
     def sync_all():
@@ -301,31 +302,47 @@ def main():
         host_out = torch.empty(G, a.hidden).pin_memory()
         d2h = host_out.numel() * 4
 
+        # The public API with a one-batch look-ahead, as a data loader would drive it: the upload + CSR build
+        # of batch i+1 run on a copy stream (DeviceGraph.prefetch) while the encoder step of batch i runs.
+        # Every step uploads one full batch from pinned host memory and reads its encoder output back.
+        copy_stream = torch.cuda.Stream(device=dev)
+
+        def next_batch():
+            hg = HostGraph(pinned)                       # fresh object: nothing cached on it
+            DeviceGraph.prefetch(hg, dev, copy_stream)
+            return hg
+
+        state = {"next": next_batch()}
+
         def e2e_step():
+            cur, state["next"] = state["next"], next_batch()
             for p in params:
                 p.grad = None
-            out = model([HostGraph(pinned)])
+            out = model([cur])
             out.backward(d_out)
             if world > 1:
-                flat = torch.cat([p.grad.reshape(-1) for p in params])
-                dist.all_reduce(flat)
+                reducer()
             host_out.copy_(out.detach(), non_blocking=True)
             torch.cuda.current_stream().synchronize()
 
         for _ in range(3):
             e2e_step()
         sync_all()
-        k = max(3, min(a.steps, 10))
+        k = max(3, min(a.steps, 20))
         t0 = time.perf_counter()
         for _ in range(k):
+            ts = time.perf_counter()
             e2e_step()
+            if os.environ.get("WD_BENCH_DEBUG"):
+                print(f"e2e step wall {1e3 * (time.perf_counter() - ts):.2f} ms", file=sys.stderr)
         sync_all()
         te = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e = {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": k,
-               "api": "MPN.forward([batch with pinned CPU tensors]) + backward + out.cpu()"}
+               "api": "DeviceGraph.prefetch(next batch of pinned CPU tensors, copy stream) || MPN.forward(batch) + "
+                      "backward + out -> pinned host"}
 
     if rank == 0:
         peak, peak_src = load_peaks()

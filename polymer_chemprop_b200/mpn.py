@@ -32,11 +32,23 @@ class DeviceGraph:
     int32 CSR / reverse-CSR arrays rebuilt on the device by wd_csr_build.  Cached on the
     BatchMolGraph instance (like the reference caches a2a / b2b, featurization.py:812-813)."""
 
-    def __init__(self, mol_graph, device: torch.device, validate: bool = True):
+    def __init__(self, mol_graph, device: torch.device, validate: bool = True, stream=None):
+        """``stream``: build on that CUDA stream without blocking the host (pinned host tensors are
+        copied with non_blocking=True); consumers wait on ``self.ready``.  Validation of the graph
+        invariants is deferred to ``check()`` (first use), which only waits for this graph's own work."""
+        if stream is not None:
+            with torch.cuda.stream(stream):
+                self._build(mol_graph, device, non_blocking=True)
+        else:
+            self._build(mol_graph, device, non_blocking=False)
+        self._validate = validate
+        self._checked = False
+
+    def _build(self, mol_graph, device, non_blocking):
         f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, a_scope, _b_scope, dop = \
             mol_graph.get_components(atom_messages=False)
-        f32 = dict(device=device, dtype=torch.float32)
-        i64 = dict(device=device, dtype=torch.int64)
+        f32 = dict(device=device, dtype=torch.float32, non_blocking=non_blocking)
+        i64 = dict(device=device, dtype=torch.int64, non_blocking=non_blocking)
         self.device = device
         self.f_atoms = f_atoms.to(**f32).contiguous()          # mpn.py:84-87
         self.f_bonds = f_bonds.to(**f32).contiguous()
@@ -54,6 +66,7 @@ class DeviceGraph:
         dop_h = torch.tensor([float(x) for x in dop], dtype=torch.float32)
         if device.type == "cuda":
             host, dop_h = host.pin_memory(), dop_h.pin_memory()
+        self._host_keepalive = (host, dop_h)                   # pinned sources of in-flight async copies
         scopes = host.to(device, non_blocking=True)
         self.a_start, self.a_size = scopes[:self.n_mols], scopes[self.n_mols:]
         self.dop = dop_h.to(device, non_blocking=True)
@@ -72,15 +85,54 @@ class DeviceGraph:
                                    p(self.a_start), p(self.a_size), self.n_mols, p(self.in_ptr),
                                    p(self.in_idx), p(self.out_idx), p(self.src), p(self.rev), p(self.dst),
                                    p(self.mol_of), p(self.flags), stream))
-        if validate:
-            _capi.check(L.wd_csr_build_check(p(self.flags), stream))
+        self._int64_keepalive = (a2b, b2a, b2revb)             # read by the CSR kernels still in flight
+        self.flags_host = torch.empty(4, dtype=torch.int32).pin_memory() if device.type == "cuda" else None
+        if self.flags_host is not None:
+            self.flags_host.copy_(self.flags, non_blocking=True)
+        self.build_stream = torch.cuda.current_stream(device)
+        self.ready = torch.cuda.Event()
+        self.ready.record(self.build_stream)
         self.struct = _capi.WdGraph(
             self.n_atoms, self.n_bonds, self.n_mols, p(self.f_atoms), p(self.f_bonds), p(self.w_atoms),
             p(self.w_bonds), p(self.in_ptr), p(self.in_idx), p(self.out_idx), p(self.src), p(self.rev),
             p(self.dst), p(self.mol_of), p(self.a_start), p(self.a_size), p(self.dop))
 
+    def tensors(self):
+        return (self.f_atoms, self.f_bonds, self.w_atoms, self.w_bonds, self.a_start, self.dop, self.in_ptr,
+                self.in_idx, self.out_idx, self.src, self.rev, self.dst, self.mol_of, self.flags)
+
+    def use_on(self, stream):
+        """Orders ``stream`` after this graph's build and tells the caching allocator that ``stream`` reads
+        the graph's buffers (they were allocated on the build stream)."""
+        stream.wait_event(self.ready)
+        if stream != self.build_stream:
+            for t in self.tensors():
+                t.record_stream(stream)
+
+    def check(self):
+        """Waits for this graph's upload + CSR build (not for the consumer stream) and raises
+        ValueError if the BatchMolGraph invariants were violated (wd_csr_build flags[0])."""
+        if self._checked:
+            return
+        self.ready.synchronize()
+        self._int64_keepalive = None
+        self._host_keepalive = None
+        if self._validate and int(self.flags_host[0]) != 0:
+            raise ValueError(f"inconsistent BatchMolGraph: {int(self.flags_host[0])} invariant violations "
+                             "(bond id out of range, bond listed in 0 or >1 a2b rows, b2revb not an involution, "
+                             "or a_scope out of range)")
+        self._checked = True
+
     @staticmethod
-    def get(mol_graph, device: torch.device) -> "DeviceGraph":
+    def prefetch(mol_graph, device: torch.device, stream) -> "DeviceGraph":
+        """Starts the host->device upload and the device CSR build of ``mol_graph`` on ``stream`` and
+        returns immediately; a later ``MPN.forward([mol_graph])`` picks the cached result up and makes
+        its own stream wait for it.  This is how a data loader overlaps the upload of batch i+1 with
+        the encoder step of batch i."""
+        return DeviceGraph.get(mol_graph, device, stream=stream)
+
+    @staticmethod
+    def get(mol_graph, device: torch.device, stream=None) -> "DeviceGraph":
         cache = getattr(mol_graph, "_wd_cache", None)
         if cache is None:
             cache = {}
@@ -90,7 +142,7 @@ class DeviceGraph:
                 pass
         key = (device.type, device.index)
         if key not in cache:
-            cache[key] = DeviceGraph(mol_graph, device)
+            cache[key] = DeviceGraph(mol_graph, device, stream=stream)
         return cache[key]
 
 
@@ -192,6 +244,8 @@ class MPNEncoder(nn.Module):
             raise RuntimeError("the B200 encoder runs on CUDA devices only (no CPU fallback); "
                                f"parameters are on {device}")
         dg = DeviceGraph.get(mol_graph, device)
+        dg.use_on(torch.cuda.current_stream(device))
+        dg.check()
         if dg.atom_fdim != self.atom_fdim or dg.bond_fdim != self.bond_fdim:
             raise ValueError(f"feature dims of the batch ({dg.atom_fdim}, {dg.bond_fdim}) do not match the "
                              f"encoder ({self.atom_fdim}, {self.bond_fdim})")

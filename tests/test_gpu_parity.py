@@ -57,7 +57,7 @@ def test_csr_rejects_inconsistent_graph():
     b2revb[3], b2revb[4] = b2revb[5].item(), b2revb[6].item()       # break the involution
     comps[6] = b2revb
     with pytest.raises(ValueError):
-        DeviceGraph(_util.ComponentsGraph(tuple(comps)), DEV)
+        DeviceGraph(_util.ComponentsGraph(tuple(comps)), DEV).check()
 
 
 @pytest.mark.parametrize("name", _golden.NAMES)
