@@ -169,6 +169,8 @@ int wd_debug_gemm(const float* A, int lda, const float* W, int ldb, int b_kn, co
                   int math_mode, void* scratch, size_t scratch_bytes, void* stream);
 int wd_debug_dw(const float* X, int ldx, const float* Y, int ldy, float* out, int64_t R, int N1, int N2,
                 int math_mode, void* scratch, size_t scratch_bytes, void* stream);
+/* Wait-cycle counters of CTA 0 of the tcgen05 GEMM kernel (zero unless built with -DWD_T2_TIMING). */
+int wd_debug_timing(uint64_t* out16, int reset);
 
 /* Thread-local message of the last failing call on this thread. */
 const char* wd_last_error(void);

@@ -46,7 +46,7 @@ class WdGrads(C.Structure):
 EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_workspace_bytes", "wd_encoder_forward",
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
-           "wd_debug_dw")
+           "wd_debug_dw", "wd_debug_timing")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
@@ -87,6 +87,8 @@ def lib():
     L.wd_debug_dw.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int64, C.c_int, C.c_int, C.c_int, vp,
                               C.c_size_t, vp]
     L.wd_debug_dw.restype = C.c_int
+    L.wd_debug_timing.argtypes = [vp, C.c_int]
+    L.wd_debug_timing.restype = C.c_int
     L.wd_last_error.restype = C.c_char_p
     L.wd_launch_count.restype = C.c_int64
     L.wd_abi_version.restype = C.c_int

@@ -418,3 +418,16 @@ extern "C" int wd_debug_dw(const float* X, int ldx, const float* Y, int ldy, flo
   WD_TRY((dw_partial<A_PLAIN, WD_ACT_RELU, false>(c, s, X, ldx, y, N2, 0, P, R, N1, Z)));
   return reduce_partials(s, P, out, (int64_t)N1 * N2, Z);
 }
+
+// Reads (and optionally clears) the per-role wait-cycle counters of CTA 0 of the tcgen05 GEMM kernel
+// (all zero unless the library was built with -DWD_T2_TIMING).
+extern "C" int wd_debug_timing(uint64_t* out16, int reset) {
+  unsigned long long h[16];
+  if (cudaMemcpyFromSymbol(h, wd::g_t2_timing, sizeof(h)) != cudaSuccess) return wd::fail(WD_ERR_CUDA, "wd_debug_timing: copy failed");
+  for (int i = 0; i < 16; ++i) out16[i] = h[i];
+  if (reset) {
+    unsigned long long z[16] = {};
+    if (cudaMemcpyToSymbol(wd::g_t2_timing, z, sizeof(z)) != cudaSuccess) return wd::fail(WD_ERR_CUDA, "wd_debug_timing: reset failed");
+  }
+  return 0;
+}

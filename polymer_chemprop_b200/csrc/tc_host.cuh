@@ -71,6 +71,7 @@ int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   const int smem = t2_smem_bytes(B.BN);
   if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 tile does not fit shared memory");
   if (EPI == E_RES_ACT && (!tc_aligned16(R, ldr))) return fail(WD_ERR_INVALID_ARG, "tcgen05 residual rows must be 16-byte aligned");
+  if (!tc_aligned16(C, ldc)) return fail(WD_ERR_INVALID_ARG, "tcgen05 output rows must be 16-byte aligned");
   auto kern = k_tc_gemm2<NSRC, EPI, ACT, PREACT>;
   int rc = tc_set_smem(kern, smem);
   if (rc != WD_OK) return rc;
