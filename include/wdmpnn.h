@@ -73,6 +73,9 @@ typedef struct WdGraph {
   const int32_t* a_start; /* [G] a_scope starts                     */
   const int32_t* a_size;  /* [G] a_scope sizes                      */
   const float* dop;       /* [G] degree_of_polym                    */
+  int32_t ld_atoms;       /* row stride of f_atoms in floats; 0 = F_a (dense, the reference layout) */
+  int32_t ld_bonds;       /* row stride of f_bonds in floats; 0 = F_b.  Strides that are multiples   */
+                          /* of 4 put the feature rows on the 16-byte asynchronous-copy path         */
 } WdGraph;
 
 /* nn.Linear layout [out, in] row-major, exactly the reference's parameters (mpn.py:47-57).

@@ -32,7 +32,7 @@ class WdGraph(C.Structure):
                 ("w_bonds", C.c_void_p), ("in_ptr", C.c_void_p), ("in_idx", C.c_void_p),
                 ("out_idx", C.c_void_p), ("src", C.c_void_p), ("rev", C.c_void_p), ("dst", C.c_void_p),
                 ("mol_of", C.c_void_p), ("a_start", C.c_void_p), ("a_size", C.c_void_p),
-                ("dop", C.c_void_p)]
+                ("dop", C.c_void_p), ("ld_atoms", C.c_int32), ("ld_bonds", C.c_int32)]
 
 
 class WdWeights(C.Structure):
@@ -50,6 +50,7 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_workspace_bytes", "wd_encod
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
+ABI_VERSION = 2      # include/wdmpnn.h: WdGraph gained ld_atoms / ld_bonds
 _lib = None
 
 
@@ -92,6 +93,8 @@ def lib():
     L.wd_last_error.restype = C.c_char_p
     L.wd_launch_count.restype = C.c_int64
     L.wd_abi_version.restype = C.c_int
+    if L.wd_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"{LIB_PATH} has ABI version {L.wd_abi_version()}, this package needs {ABI_VERSION}: rebuild it")
     L.wd_profile_enable.argtypes = [C.c_int]
     L.wd_profile_enable.restype = None
     L.wd_profile_reset.restype = None

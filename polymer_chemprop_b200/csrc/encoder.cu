@@ -101,6 +101,8 @@ int check_graph(const WdGraph* g, const WdWeights* w, const WdConfig* c) {
       !g->dst || !g->mol_of || (g->n_bonds > 1 && (!g->in_idx || !g->out_idx)) ||
       (g->n_mols > 0 && (!g->a_start || !g->a_size || !g->dop)))
     return fail(WD_ERR_INVALID_ARG, "graph has NULL device pointers");
+  if ((g->ld_atoms && g->ld_atoms < c->atom_fdim) || (g->ld_bonds && g->ld_bonds < c->bond_fdim))
+    return fail(WD_ERR_INVALID_ARG, "ld_atoms / ld_bonds must be 0 or >= atom_fdim / bond_fdim");
   if (!w->W_i || !w->W_h || !w->W_o || !w->b_o || (c->bias && (!w->b_i || !w->b_h)))
     return fail(WD_ERR_INVALID_ARG, "weights have NULL device pointers");
   return WD_OK;
@@ -171,7 +173,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     WD_TRY(tc_pack(s, w.W_o, Fa + h, B_NK, L.pWo));
   }
   // input = W_i(f_bonds)                                                      mpn.py:96
-  AOperand a_in{g.f_bonds, nullptr, nullptr, nullptr, Fb, 0, 0};
+  AOperand a_in{g.f_bonds, nullptr, nullptr, nullptr, g.ld_bonds ? g.ld_bonds : Fb, 0, 0};
   { ProfScope ps(WD_PROF_INPUT_PROJ);
   WD_TRY((gemm<A_PLAIN, B_NK, E_STORE, ACT, false>(c, s, a_in, w.W_i, Fb, c.bias ? w.b_i : nullptr, nullptr, 0,
                                                   I, ld, Nb, h, Fb, &L.pWi))); }
@@ -207,7 +209,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   if (c.depth == 1) WD_LAUNCH((k_aggregate<ACT, true>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4);
   else              WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4); }
   float* H = L.p(ws, L.H);
-  AOperand a_o{g.f_atoms, A_d, nullptr, nullptr, Fa, ld, Fa};
+  AOperand a_o{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
   { ProfScope ps(WD_PROF_ATOM_UPDATE);
   WD_TRY((gemm<A_CONCAT, B_NK, E_ACT, ACT, false>(c, s, a_o, w.W_o, Fa + h, w.b_o, nullptr, 0, H, ld, Na, h, Fa + h, &L.pWo))); }
   // readout                                                                          :146-171
@@ -263,7 +265,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zo;
-    AOperand y{g.f_atoms, A_d, nullptr, nullptr, Fa, ld, Fa};
+    AOperand y{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
     WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, P, Na, h, Z)));
     WD_TRY(reduce_partials(s, P, gr.dW_o, (int64_t)h * Fo, Z));
     WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, Z));
@@ -317,7 +319,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   {  // dW_i = dI^T f_bonds ; db_i = colsum(dI)
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zi;
-    AOperand y{g.f_bonds, nullptr, nullptr, nullptr, Fb, 0, 0};
+    AOperand y{g.f_bonds, nullptr, nullptr, nullptr, g.ld_bonds ? g.ld_bonds : Fb, 0, 0};
     WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s, dI, ld, y, Fb, 0, P, Nb, h, Z)));
     WD_TRY(reduce_partials(s, P, gr.dW_i, (int64_t)h * Fb, Z));
     if (c.bias && gr.db_i) WD_TRY(colsum(s, dI, ld, Pcol, gr.db_i, Nb, h, Z));
@@ -369,7 +371,7 @@ extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weight
 
 extern "C" const char* wd_last_error(void) { return wd::g_err; }
 extern "C" int64_t wd_launch_count(void) { return wd::g_launches.load(); }
-extern "C" int wd_abi_version(void) { return 1; }
+extern "C" int wd_abi_version(void) { return 2; }
 
 // ---- test hooks: the raw contractions behind the encoder, on plain operands ----------------------
 // C[M, ldc] = epi(A[M, K] * B^T (+ bias) (+ R)), B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k].

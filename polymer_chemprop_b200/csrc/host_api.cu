@@ -26,6 +26,17 @@ struct DeviceArena {  // stream-ordered scratch, released in the destructor
     if (e != cudaSuccess || n == 0) return e;
     return cudaMemcpyAsync(*out, host, n * sizeof(T), cudaMemcpyHostToDevice, s);
   }
+  // dense host rows [n, f] -> device rows of stride ld >= f (pad columns zeroed): feature rows land on
+  // 16-byte boundaries, which is what the asynchronous-copy loaders of the tensor-core kernels want
+  cudaError_t upload_rows(float** out, const float* host, size_t n, int f, int ld) {
+    if (ld == f) return upload(out, host, n * f);
+    cudaError_t e = alloc(out, n * ld);
+    if (e != cudaSuccess || n == 0) return e;
+    e = cudaMemsetAsync(*out, 0, n * ld * sizeof(float), s);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpy2DAsync(*out, (size_t)ld * sizeof(float), host, (size_t)f * sizeof(float), (size_t)f * sizeof(float), n,
+                             cudaMemcpyHostToDevice, s);
+  }
 };
 
 }  // namespace
@@ -61,8 +72,9 @@ extern "C" int wd_encoder_host(const float* f_atoms, const float* f_bonds, const
   int64_t *d_a2b, *d_b2a, *d_rev;
   int32_t *d_start, *d_size, *in_ptr, *in_idx, *out_idx, *src, *rev, *dst, *mol_of, *flags;
   void* ws;
-  WD_CUDA_OK(A.upload(&d_fa, f_atoms, (size_t)Na * Fa));
-  WD_CUDA_OK(A.upload(&d_fb, f_bonds, (size_t)Nb * Fb));
+  const int lda = (Fa + 3) & ~3, ldb = (Fb + 3) & ~3;
+  WD_CUDA_OK(A.upload_rows(&d_fa, f_atoms, (size_t)Na, Fa, lda));
+  WD_CUDA_OK(A.upload_rows(&d_fb, f_bonds, (size_t)Nb, Fb, ldb));
   WD_CUDA_OK(A.upload(&d_wa, w_atoms, (size_t)Na));
   WD_CUDA_OK(A.upload(&d_wb, w_bonds, (size_t)Nb));
   WD_CUDA_OK(A.upload(&d_a2b, a2b, (size_t)Na * K));
@@ -103,6 +115,7 @@ extern "C" int wd_encoder_host(const float* f_atoms, const float* f_bonds, const
   if (rc != WD_OK) return rc;
   dg.n_atoms = Na; dg.n_bonds = Nb; dg.n_mols = G;
   dg.f_atoms = d_fa; dg.f_bonds = d_fb; dg.w_atoms = d_wa; dg.w_bonds = d_wb;
+  dg.ld_atoms = lda; dg.ld_bonds = ldb;
   dg.in_ptr = in_ptr; dg.in_idx = in_idx; dg.out_idx = out_idx; dg.src = src; dg.rev = rev; dg.dst = dst;
   dg.mol_of = mol_of; dg.a_start = d_start; dg.a_size = d_size; dg.dop = d_dop;
 

@@ -92,6 +92,8 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
   uint8_t* raw = opA + D3_OP_STAGES * op_stage;
   float* epi_st = reinterpret_cast<float*>(raw + SR * raw_stage);
   D3Barriers* bar = reinterpret_cast<D3Barriers*>(raw + SR * raw_stage + TC_EPI_STAGE_BYTES);
+  long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // WD_T2_TIMING: 0 xform<-raw_full 1 xform<-op_empty 2 loader<-raw_empty
+  const long long t_start = clock64();                   //               5 mma<-op_full 7 epi<-tmem_full
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < SR; ++s) { ptx::mbar_init(&bar->raw_full[s], D3_LOAD_THREADS); ptx::mbar_init(&bar->raw_empty[s], D3_XFORM_WARPS); }
@@ -124,8 +126,8 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
     const int xtasks = (p.xw / 32) * 4, ytasks = (int)ceil_div(tl.BN, 32) * 4;
     for (int kc = 0; kc < KC; ++kc) {
       const int s = kc % SR, os = kc % D3_OP_STAGES;
-      ptx::mbar_wait(&bar->raw_full[s], (kc / SR) & 1);
-      ptx::mbar_wait(&bar->op_empty[os], ((kc / D3_OP_STAGES) & 1) ^ 1);
+      T2_WAIT(0, &bar->raw_full[s], (kc / SR) & 1);
+      T2_WAIT(1, &bar->op_empty[os], ((kc / D3_OP_STAGES) & 1) ^ 1);
       const uint8_t* rx = raw + s * raw_stage;
       const uint8_t* ry = rx + x_raw;
       uint8_t* oa = opA + os * op_stage;
@@ -177,7 +179,7 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
       const bool ok = r < r_end;
       int64_t ra = ok ? r : 0, rb = ra;
       if (ok && indirect) { ra = __ldg(p.i0 + r); if (NSRC == 2) rb = __ldg(p.i1 + r); }
-      ptx::mbar_wait(&bar->raw_empty[s], ((kc / SR) & 1) ^ 1);
+      T2_WAIT(2, &bar->raw_empty[s], ((kc / SR) & 1) ^ 1);
       const uint32_t dx = raw_u32 + s * raw_stage + rl * xstride;
       const uint32_t dy = raw_u32 + s * raw_stage + x_raw + rl * ystride;
       const float* xrow = p.X + (ok ? r : 0) * p.ldx + n1_0;
@@ -206,7 +208,7 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
     const uint32_t idesc = ptx::idesc_tf32(128, tl.BN);
     for (int kc = 0; kc < KC; ++kc) {
       const int os = kc % D3_OP_STAGES;
-      ptx::mbar_wait(&bar->op_full[os], (kc / D3_OP_STAGES) & 1);
+      T2_WAIT(5, &bar->op_full[os], (kc / D3_OP_STAGES) & 1);
       ptx::tc_fence_after();
       if (lane == 0) {
         const uint32_t a_addr = ptx::smem_u32(opA + os * op_stage), b_addr = a_addr + D3_A_STAGE;
@@ -223,7 +225,7 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
       __syncwarp();
     }
   } else if (warp < T2_EPI_WARPS) {
-    ptx::mbar_wait(&bar->tmem_full, 0);
+    T2_WAIT(7, &bar->tmem_full, 0);
     ptx::tc_fence_after();
     float* Pz = p.P + (int64_t)blockIdx.y * p.N1 * p.ldp;
     for (int mt = 0; mt < n_mt; ++mt)
@@ -231,6 +233,15 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
                                 n1_0 + mt * TC_BM, p.N1, tl.out_col0, tl.out_col0 + tl.width, tl.out_col0 + tl.width,
                                 nullptr, nullptr, 0, Pz, p.ldp);
   }
+#ifdef WD_T2_TIMING
+  if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
+    if (warp == 0 || warp == T2_MMA_WARP || warp == 6 || warp == D3_XFORM_W0)
+      for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
+    if (warp == 0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));
+  }
+#else
+  (void)tacc; (void)t_start;
+#endif
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == T2_MMA_WARP) {

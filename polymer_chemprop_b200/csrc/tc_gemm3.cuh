@@ -1,0 +1,142 @@
+// tcgen05 contraction kernel, third generation, for PLAIN / CONCAT A operands (no gather):
+//
+//   C[M, ldc] = epi( A * B^T ),  A = [X0 | X1] row-major matrices with 16-byte aligned rows
+//
+// The second generation moved every A byte with cp.async (LDGSTS: measured ~12 bytes / cycle / SM, the binding
+// limit once the epilogue was fixed) and then through a transform pass (round to TF32, swizzle).  A plain
+// matrix needs neither: a TMA tensor copy (box 128 rows x 32 columns, SWIZZLE_128B) writes the K-major operand
+// stage directly and its TFLOAT32 data type rounds fp32 -> tf32 in flight.  One producer lane issues the A box
+// and the bulk copy of the packed weight chunk on one mbarrier; tcgen05.mma consumes it; the epilogue
+// (t2_epilogue) overlaps the next tile through the second TMEM accumulator.
+//   warps 0-3 epilogue, warp 4 MMA issue, warp 5 producer.
+#pragma once
+#include "tc_gemm2.cuh"
+#include "tc_tma.cuh"
+
+namespace wd {
+
+constexpr int T3_STAGES = 4;
+constexpr int T3_PROD_WARP = 5;
+constexpr int T3_THREADS = 32 * 6;
+
+struct T3Barriers {
+  uint64_t full[T3_STAGES], empty[T3_STAGES];
+  uint64_t tmem_full[2], tmem_empty[2];
+  uint64_t r_dummy[2 * T2_R_SLOTS];   // t2_epilogue's residual barriers (unused: EPI != E_RES_ACT here)
+  uint32_t tmem_base;
+};
+
+struct T3Params {
+  CUtensorMap ma[2];    // K segments of A (box 128 x 32, SWIZZLE_128B, TFLOAT32)
+  int KC0, KC;          // chunks of segment 0 / total
+  const float* Bp;
+  const float* bias;
+  float* C;
+  int ldc;
+  int64_t M;
+  int N, BN, n_tiles;
+};
+
+inline int t3_smem_bytes(int BN) {
+  return 1024 + T3_STAGES * (TC_A_STAGE + BN * 128) + T2_R_BYTES + (int)sizeof(T2Barriers) + (int)sizeof(T3Barriers) + 64;
+}
+
+template <int EPI, int ACT>
+__global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constant__ T3Params p) {
+  static_assert(EPI != E_RES_ACT, "the residual epilogue belongs to the gathered kernel");
+  extern __shared__ uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = ptx::smem_u32(smem_raw);
+  uint8_t* ops = smem_raw + (((base + 1023u) & ~1023u) - base);        // 1024-aligned
+  const int b_stage = p.BN * 128, stage = TC_A_STAGE + b_stage;          // multiples of 1024 (BN % 16 == 0 -> 2048)
+  uint8_t* rring = ops + T3_STAGES * stage;
+  T2Barriers* ebar = reinterpret_cast<T2Barriers*>(rring + T2_R_BYTES);  // only handed to t2_epilogue
+  T3Barriers* bar = reinterpret_cast<T3Barriers*>(ebar + 1);
+  long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // WD_T2_TIMING: 3 producer<-empty 4 mma<-tmem_empty 5 mma<-full 7 epi<-tmem_full
+  const long long t_start = clock64();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < T3_STAGES; ++s) { ptx::mbar_init(&bar->full[s], 1); ptx::mbar_init(&bar->empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(&bar->tmem_full[a], 1); ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS); }
+    ptx::fence_barrier_init();
+    ptx::tma_prefetch_desc(&p.ma[0]);
+  }
+  if (warp == T2_MMA_WARP) ptx::tmem_alloc(&bar->tmem_base, TC_TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = bar->tmem_base;
+  const int64_t total = ceil_div(p.M, TC_BM) * p.n_tiles;
+
+  if (warp == T3_PROD_WARP) {
+    // ================= producer: A box by TMA + packed weight chunk by bulk copy, one barrier per stage =================
+    if (lane == 0) {
+      uint32_t it = 0;
+      const uint32_t bytes = (uint32_t)stage;
+      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int row0 = (int)((tile / p.n_tiles) * TC_BM);
+        const int nt = (int)(tile % p.n_tiles);
+        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+          const int s = it % T3_STAGES;
+          T2_WAIT(3, &bar->empty[s], ((it / T3_STAGES) & 1) ^ 1);
+          ptx::mbar_arrive_expect_tx(&bar->full[s], bytes);
+          const bool second = kc >= p.KC0;
+          ptx::tma_load_2d(ops + s * stage, &p.ma[second ? 1 : 0], (second ? kc - p.KC0 : kc) * TC_BK, row0, &bar->full[s]);
+          ptx::bulk_g2s(ops + s * stage + TC_A_STAGE, p.Bp + ((int64_t)nt * p.KC + kc) * p.BN * 32, (uint32_t)b_stage, &bar->full[s]);
+        }
+      }
+    }
+  } else if (warp == T2_MMA_WARP) {
+    // ================= MMA issue =================
+    uint32_t it = 0, tl = 0;
+    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x, ++tl) {
+      const int acc = tl & 1;
+      T2_WAIT(4, &bar->tmem_empty[acc], ((tl >> 1) & 1) ^ 1);
+      ptx::tc_fence_after();
+      for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        const int s = it % T3_STAGES;
+        T2_WAIT(5, &bar->full[s], (it / T3_STAGES) & 1);
+        ptx::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = ptx::smem_u32(ops + s * stage);
+          tc_issue_chunk(a_addr, a_addr + TC_A_STAGE, tmem_base + acc * 256, p.BN, kc == 0);
+          ptx::tc_commit(&bar->empty[s]);
+          if (kc == p.KC - 1) ptx::tc_commit(&bar->tmem_full[acc]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp < T2_EPI_WARPS) {
+    // ================= epilogue =================
+    uint32_t tl = 0, rit = 0;
+    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x, ++tl) {
+      const int acc = tl & 1;
+      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+      const int col0 = (int)(tile % p.n_tiles) * p.BN;
+      T2_WAIT(7, &bar->tmem_full[acc], (tl >> 1) & 1);
+      ptx::tc_fence_after();
+      t2_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, ebar, rit, p.BN, row0, p.M, col0, p.N, p.ldc,
+                            p.bias, p.C, p.ldc, tacc);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);
+    }
+  }
+#ifdef WD_T2_TIMING
+  if (blockIdx.x == 0 && lane == 0) {
+    if (warp == 0 || warp == T2_MMA_WARP || warp == T3_PROD_WARP)
+      for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
+    if (warp == 0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));
+  }
+#else
+  (void)tacc; (void)t_start;
+#endif
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == T2_MMA_WARP) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
+  }
+}
+
+}  // namespace wd

@@ -1,8 +1,11 @@
 // Host-side launch helpers of the tcgen05 contraction kernels (tc_gemm.cuh / tc_dw.cuh).
 #pragma once
+#include "tc_gemm3.cuh"
 #include "tc_dw.cuh"
 #include "tc_dw2.cuh"
 #include "tc_dw3.cuh"
+#include "tc_dw4.cuh"
+#include "tc_dw5.cuh"
 #include "tc_gemm2.cuh"
 
 namespace wd {
@@ -19,8 +22,8 @@ inline bool tc_use_v1() {   // WD_TC_V1=1: first-generation (register-staged) ke
   return v;
 }
 
-inline int tc_dw_version() {   // WD_TC_DW=1|2|3: generation of the dW kernel (default 3), for A/B comparisons
-  static int v = [] { const char* e = getenv("WD_TC_DW"); int x = e ? atoi(e) : 3; return (x >= 1 && x <= 3) ? x : 3; }();
+inline int tc_dw_version() {   // WD_TC_DW=1..5: generation of the dW kernel (default 5), for A/B comparisons
+  static int v = [] { const char* e = getenv("WD_TC_DW"); int x = e ? atoi(e) : 5; return (x >= 1 && x <= 5) ? x : 5; }();
   return tc_use_v1() ? 1 : v;
 }
 
@@ -81,11 +84,69 @@ int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   return WD_OK;
 }
 
+inline bool tc_use_gemm3() {   // WD_TC_GEMM=2 keeps plain operands on the second-generation (cp.async) kernel
+  static bool v = [] { const char* e = getenv("WD_TC_GEMM"); return !(e && atoi(e) == 2); }();
+  return v;
+}
+
+// third-generation kernel for plain / concatenated A operands: TMA tensor copies, no transform pass
+template <int AMODE, int EPI, int ACT>
+int tc_gemm3(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, float* C, int ldc, int64_t M) {
+  T3Params p{};
+  int rc = tma_make_2d(&p.ma[0], A.X, M, B.K1, A.ldx, TC_BM, TMA_SW128);
+  if (rc != WD_OK) return rc;
+  if (AMODE == A_CONCAT) {
+    rc = tma_make_2d(&p.ma[1], A.X2, M, B.K2, A.ldx2, TC_BM, TMA_SW128);
+    if (rc != WD_OK) return rc;
+  }
+  p.KC0 = B.KC1; p.KC = B.KC;
+  p.Bp = B.img; p.bias = bias; p.C = C; p.ldc = ldc; p.M = M;
+  p.N = B.N; p.BN = B.BN; p.n_tiles = B.n_tiles;
+  const int smem = t3_smem_bytes(B.BN);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 tile does not fit shared memory");
+  auto kern = k_tc_gemm3<EPI, ACT>;
+  rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  const int64_t tiles = ceil_div(M, TC_BM) * B.n_tiles;
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
+  WD_LAUNCH(kern, grid, T3_THREADS, smem, s, p);
+  return WD_OK;
+}
+
+template <int AMODE, int EPI, int ACT, bool PREACT>
+struct TcGemm3Dispatch {   // the TMA kernel exists for plain operands and the store / activation epilogues only
+  static int run(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, float* C, int ldc, int64_t M) {
+    return tc_gemm3<AMODE, EPI, ACT>(s, A, B, bias, C, ldc, M);
+  }
+  static constexpr bool ok = true;
+};
+template <int EPI, int ACT, bool PREACT>
+struct TcGemm3Dispatch<A_GATHER_DIFF, EPI, ACT, PREACT> {
+  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t) { return WD_ERR_UNSUPPORTED; }
+  static constexpr bool ok = false;
+};
+template <int AMODE, int ACT, bool PREACT>
+struct TcGemm3Dispatch<AMODE, E_RES_ACT, ACT, PREACT> {
+  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t) { return WD_ERR_UNSUPPORTED; }
+  static constexpr bool ok = false;
+};
+template <int ACT, bool PREACT>
+struct TcGemm3Dispatch<A_GATHER_DIFF, E_RES_ACT, ACT, PREACT> {
+  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t) { return WD_ERR_UNSUPPORTED; }
+  static constexpr bool ok = false;
+};
+
 // C[M, ldc] = epi( A[M, K1+K2] * B^T ) with B packed
 template <int AMODE, int EPI, int ACT, bool PREACT>
 int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
             float* C, int ldc, int64_t M) {
-  if (!tc_use_v1()) return tc_gemm2<AMODE, EPI, ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M);
+  if (!tc_use_v1()) {
+    using D3 = TcGemm3Dispatch<AMODE, EPI, ACT, PREACT>;
+    if (D3::ok && tc_use_gemm3() && B.BN <= T2_MAX_BN && tc_aligned16(A.X, A.ldx) && tc_aligned16(C, ldc) &&
+        (AMODE != A_CONCAT || tc_aligned16(A.X2, A.ldx2)))
+      return D3::run(s, A, B, bias, C, ldc, M);
+    return tc_gemm2<AMODE, EPI, ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M);
+  }
   TcGemmParams p{};
   p.A = A;
   p.A.K1 = B.K1;
@@ -139,7 +200,7 @@ inline int tc_dw_count_tiles(int w0, int w1) {
 
 // number of row chunks so that the grid roughly fills the GPU once
 inline int tc_dw_z(int64_t rows, int n1, int n2_tiles) {
-  const int64_t ctas = ceil_div(n1, tc_dw_version() == 3 ? D3_MROWS : TC_BM) * std::max(1, n2_tiles);
+  const int64_t ctas = ceil_div(n1, tc_dw_version() >= 3 ? D3_MROWS : TC_BM) * std::max(1, n2_tiles);
   int64_t z = std::max<int64_t>(1, kNumSMs / ctas);
   z = std::min<int64_t>(z, std::max<int64_t>(1, rows / 128));
   z = std::min<int64_t>(z, kNumSMs);
@@ -218,10 +279,94 @@ int tc_dw3(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, i
   return WD_OK;
 }
 
+// fourth-generation dW kernel (MN-major operand stages written directly by the loaders, in-place TF32 rounding)
+template <int YMODE, int ACT, bool PREACT>
+int tc_dw4(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
+           int Z) {
+  constexpr int NSRC = YMODE == A_GATHER_DIFF ? 2 : 1;
+  D4Params p{};
+  if (!tc_aligned16(X, ldx)) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: X rows must be 16-byte aligned");
+  p.X = X; p.ldx = ldx; p.N1 = N1; p.P = P; p.ldp = w0 + w1; p.R = R;
+  p.Y0[0] = Y.X; p.ldy[0] = Y.ldx; p.align16[0] = tc_aligned16(Y.X, Y.ldx) ? 1 : 0;
+  if (YMODE == A_GATHER_DIFF) {
+    p.Y1 = Y.X2; p.ldy1 = Y.ldx2; p.i0 = Y.src; p.i1 = Y.rev;
+    if (!p.align16[0] || !tc_aligned16(Y.X2, Y.ldx2))
+      return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: gather operand needs 16-byte aligned rows");
+  } else if (YMODE == A_CONCAT) {
+    p.Y0[1] = Y.X2; p.ldy[1] = Y.ldx2; p.align16[1] = tc_aligned16(Y.X2, Y.ldx2) ? 1 : 0;
+  }
+  p.n2_tiles = tc_dw_tiles(w0, w1, p.t);
+  if (p.n2_tiles <= 0) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW: too many column tiles");
+  p.n1_groups = (int)ceil_div(N1, D4_MROWS);
+  p.rows_per_z = round_up(ceil_div(R, Z), TC_BK);
+  if (ceil_div(R, p.rows_per_z) != Z) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: inconsistent row chunking");
+  int maxBN = 16;
+  for (int i = 0; i < p.n2_tiles; ++i) maxBN = std::max(maxBN, p.t[i].BN);
+  p.XB = (int)ceil_div(std::min(N1, D4_MROWS), 32);
+  p.YB = (int)ceil_div(maxBN, 32);
+  p.stages = D4_MAX_STAGES;
+  while (p.stages > 2 && d4_smem_bytes(p.XB, p.YB, NSRC, p.stages) > TC_SMEM_LIMIT) --p.stages;
+  const int smem = d4_smem_bytes(p.XB, p.YB, NSRC, p.stages);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW tile does not fit shared memory");
+  auto kern = k_tc_dw4<NSRC, ACT, PREACT>;
+  int rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  dim3 grid((unsigned)(p.n1_groups * p.n2_tiles), (unsigned)Z);
+  WD_LAUNCH(kern, grid, D4_THREADS, smem, s, p);
+  return WD_OK;
+}
+
+// fifth-generation dW kernel: TMA tensor copies (rounding to tf32 in flight) for X and a plain Y; needs 16-byte
+// aligned rows everywhere, otherwise the caller falls back to generation 4
+template <int YMODE, int ACT, bool PREACT>
+int tc_dw5(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
+           int Z) {
+  constexpr int NSRC = YMODE == A_GATHER_DIFF ? 2 : 1;
+  constexpr int BK = d5_bk(NSRC);
+  D5Params p{};
+  p.N1 = N1; p.P = P; p.ldp = w0 + w1; p.R = R;
+  int rc = tma_make_2d(&p.mx, X, R, N1, ldx, BK, TMA_SW128_ATOM32);
+  if (rc != WD_OK) return rc;
+  if (YMODE == A_GATHER_DIFF) {
+    p.Y0 = Y.X; p.ldy0 = Y.ldx; p.Y1 = Y.X2; p.ldy1 = Y.ldx2; p.i0 = Y.src; p.i1 = Y.rev;
+  } else {
+    rc = tma_make_2d(&p.my[0], Y.X, R, w0, Y.ldx, BK, TMA_SW128_ATOM32);
+    if (rc != WD_OK) return rc;
+    if (YMODE == A_CONCAT) {
+      rc = tma_make_2d(&p.my[1], Y.X2, R, w1, Y.ldx2, BK, TMA_SW128_ATOM32);
+      if (rc != WD_OK) return rc;
+    }
+  }
+  p.n2_tiles = tc_dw_tiles(w0, w1, p.t);
+  if (p.n2_tiles <= 0) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW: too many column tiles");
+  p.n1_groups = (int)ceil_div(N1, D4_MROWS);
+  p.rows_per_z = round_up(ceil_div(R, Z), TC_BK);
+  if (ceil_div(R, p.rows_per_z) != Z) return fail(WD_ERR_INVALID_ARG, "tcgen05 dW: inconsistent row chunking");
+  int maxBN = 16;
+  for (int i = 0; i < p.n2_tiles; ++i) maxBN = std::max(maxBN, p.t[i].BN);
+  p.XB = (int)ceil_div(std::min(N1, D4_MROWS), 32);
+  p.YB = (int)ceil_div(maxBN, 32);
+  p.stages = D5_MAX_STAGES;
+  while (p.stages > 2 && d5_smem_bytes(p.XB, p.YB, NSRC, p.stages) > TC_SMEM_LIMIT) --p.stages;
+  const int smem = d5_smem_bytes(p.XB, p.YB, NSRC, p.stages);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 dW tile does not fit shared memory");
+  auto kern = k_tc_dw5<NSRC, ACT, PREACT>;
+  rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  dim3 grid((unsigned)(p.n1_groups * p.n2_tiles), (unsigned)Z);
+  WD_LAUNCH(kern, grid, d5_threads(NSRC), smem, s, p);
+  return WD_OK;
+}
+
 // P[0..Z) <- partial X^T Y over Z row chunks (Z from tc_dw_z)
 template <int YMODE, int ACT, bool PREACT>
 int tc_dw(cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1, float* P, int64_t R, int N1,
           int Z) {
+  if (tc_dw_version() == 5) {
+    const bool aligned = tc_aligned16(X, ldx) && tc_aligned16(Y.X, Y.ldx) && (YMODE == A_PLAIN || tc_aligned16(Y.X2, Y.ldx2));
+    if (aligned) return tc_dw5<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
+  }
+  if (tc_dw_version() >= 4) return tc_dw4<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
   if (tc_dw_version() == 3) return tc_dw3<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
   if (tc_dw_version() == 2) return tc_dw2<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
   TcDwParams p{};

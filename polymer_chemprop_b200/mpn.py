@@ -50,15 +50,15 @@ class DeviceGraph:
         f32 = dict(device=device, dtype=torch.float32, non_blocking=non_blocking)
         i64 = dict(device=device, dtype=torch.int64, non_blocking=non_blocking)
         self.device = device
-        self.f_atoms = f_atoms.to(**f32).contiguous()          # mpn.py:84-87
-        self.f_bonds = f_bonds.to(**f32).contiguous()
+        self.f_atoms = self._padded_rows(f_atoms.to(**f32))    # mpn.py:84-87
+        self.f_bonds = self._padded_rows(f_bonds.to(**f32))
         self.w_atoms = w_atoms.to(**f32).contiguous()
         self.w_bonds = w_bonds.to(**f32).contiguous()
         a2b = a2b.to(**i64).contiguous()
         b2a = b2a.to(**i64).contiguous()
         b2revb = b2revb.to(**i64).contiguous()
         self.n_atoms, self.n_bonds, self.n_mols = self.f_atoms.shape[0], self.f_bonds.shape[0], len(a_scope)
-        self.atom_fdim, self.bond_fdim = self.f_atoms.shape[1], self.f_bonds.shape[1]
+        self.atom_fdim, self.bond_fdim = f_atoms.shape[1], f_bonds.shape[1]
         if a2b.dim() != 2 or a2b.shape[0] != self.n_atoms:
             raise ValueError("a2b must be [n_atoms, max_num_bonds]")
         scope = np.asarray(a_scope, dtype=np.int64).reshape(-1, 2)
@@ -95,7 +95,21 @@ class DeviceGraph:
         self.struct = _capi.WdGraph(
             self.n_atoms, self.n_bonds, self.n_mols, p(self.f_atoms), p(self.f_bonds), p(self.w_atoms),
             p(self.w_bonds), p(self.in_ptr), p(self.in_idx), p(self.out_idx), p(self.src), p(self.rev),
-            p(self.dst), p(self.mol_of), p(self.a_start), p(self.a_size), p(self.dop))
+            p(self.dst), p(self.mol_of), p(self.a_start), p(self.a_size), p(self.dop),
+            self.f_atoms.shape[1], self.f_bonds.shape[1])
+
+    @staticmethod
+    def _padded_rows(x: torch.Tensor) -> torch.Tensor:
+        """Device copy of a feature matrix whose row stride is a multiple of 4 floats (WdGraph.ld_atoms /
+        ld_bonds): 133- and 147-float rows are only 4-byte aligned, padded rows take the 16-byte
+        asynchronous-copy path of the tensor-core kernels.  Pad columns are zero and never read as data."""
+        f = x.shape[1]
+        ld = (f + 3) // 4 * 4
+        if ld == f:
+            return x.contiguous()
+        out = torch.zeros((x.shape[0], ld), dtype=x.dtype, device=x.device)
+        out[:, :f].copy_(x)
+        return out
 
     def tensors(self):
         return (self.f_atoms, self.f_bonds, self.w_atoms, self.w_bonds, self.a_start, self.dop, self.in_ptr,

@@ -37,7 +37,31 @@ def run(M, N, K, epi):
         print(f"   {n:20s} {100.0 * buf[i] / tot:6.1f}% of kernel")
 
 
+def run_dw(Rn, N1, N2):
+    X = torch.randn(Rn, (N1 + 7) // 8 * 8, device=DEV)
+    Y = torch.randn(Rn, (N2 + 3) // 4 * 4, device=DEV)
+    out = torch.empty(N1, N2, device=DEV)
+    scratch = torch.empty(160 * N1 * N2 * 4, dtype=torch.uint8, device=DEV)
+    buf = (C.c_uint64 * 16)()
+    for it in range(3):
+        L.wd_debug_timing(buf, 1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _capi.check(L.wd_debug_dw(p(X), X.stride(0), p(Y), Y.stride(0), p(out), Rn, N1, N2, 1, p(scratch), scratch.numel(),
+                                  _capi.current_stream(DEV)))
+        e1.record()
+        torch.cuda.synchronize()
+    L.wd_debug_timing(buf, 0)
+    tot = buf[15] or 1
+    print(f"dW R={Rn} N1={N1} N2={N2}: {e0.elapsed_time(e1) * 1e3:.0f} us (incl. reduce), CTA0 cycles {tot}")
+    for i, n in ((0, "xform<-raw_full"), (2, "loader<-empty"), (3, "tma<-empty"), (5, "mma<-full"), (6, "mma<-op_full"),
+                 (7, "epi<-tmem_full")):
+        print(f"   {n:20s} {100.0 * buf[i] / tot:6.1f}% of kernel")
+
+
 if __name__ == "__main__":
+    run_dw(269541, 300, 300)
+    run_dw(269541, 300, 147)
     run(269541, 300, 300, 0)
     run(269541, 300, 300, 2)
     run(269541, 300, 147, 0)
