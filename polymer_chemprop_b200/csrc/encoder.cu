@@ -19,6 +19,7 @@ struct Layout {
   int ldh;                 // row stride of every [*, h] activation buffer (h rounded up to 4)
   int64_t szB, szA;        // floats per [N_b, ldh] / [N_a, ldh] buffer
   int64_t I, M, Agg, H, mscale, U, dZ, dS, dI, dA, dZo, partials, total;
+  int64_t S;               // TF32 mode: S_t = A_t[b2a] - M_{t-1}[b2revb] written by the forward depth steps, read by dW_h
   int Z;                   // max row chunks of the weight-gradient contractions (sizes `partials`)
   int Zh, Zi, Zo;          // row chunks of the dW_h / dW_i / dW_o contractions
   TcPacked pWi, pWh, pWo, pWhT, pWoT;   // TF32 mode: packed weight images (img == offset holder until bound)
@@ -49,6 +50,7 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   L.H = take(L.szA);
   L.mscale = take(G);
   L.U = take(c.undirected ? L.szB : 0);
+  L.S = take(c.math_mode == WD_MATH_TF32 ? (int64_t)std::max(0, c.depth - 1) * L.szB : 0);
   L.dZ = take(L.szB);
   L.dS = take(L.szB);
   L.dI = take(L.szB);
@@ -69,7 +71,7 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
                                  (int64_t)h * std::max(Fo, c.bond_fdim));
   L.partials = take((int64_t)L.Z * pw + (int64_t)kColsumMaxChunks * h);
   L.pWi = tc_packed_geometry(h, c.bond_fdim, 0);     // I = f_bonds W_i^T
-  L.pWh = tc_packed_geometry(h, h, 0);               // S W_h^T
+  L.pWh = tc_packed_geometry(h, h, 0, tc_use_gemm4() ? T4_MAX_BN : T2_MAX_BN);   // S W_h^T (gathered depth step)
   L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
   L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h
   L.pWoT = tc_packed_geometry(h, h, 0);              // dA_d = dZo W_o[:, F_a:]
@@ -198,6 +200,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     ProfScope ps(WD_PROF_DEPTH_STEP);
     // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
     AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
+    if (c.math_mode == WD_MATH_TF32 && !tc_use_v1()) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
     const float* bh = c.bias ? w.b_h : nullptr;
     if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh)));
     else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh)));
@@ -284,10 +287,11 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     // dZ_t = dM_t * act'(M_t), dI += dZ_t ; dM_t = w_b dA[dst b] - dS[rev b] (symmetrised if undirected)
     if (t == d - 1) WD_TRY((message_grad<ACT, false, false, true>(c, s, g, dA, dS, M_t, ld, dZ, dI)));
     else            WD_TRY((message_grad<ACT, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, dI)));
-    // dW_h += dZ_t^T S_t, with S_t = A_t[b2a] - U_{t-1}[b2revb] recomputed, never stored
+    // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
     const float* u = M_prev;
     bool upre = pre;
-    if (c.undirected) {
+    const bool have_S = c.math_mode == WD_MATH_TF32 && !tc_use_v1();   // forward kept S_t (tensor-core path)
+    if (c.undirected && !have_S) {
       float* U = L.p(ws, L.U);
       if (pre) WD_LAUNCH((k_symmetrize<ACT, true>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
       else     WD_LAUNCH((k_symmetrize<ACT, false>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
@@ -297,7 +301,10 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     AOperand y{A_t, u, g.src, g.rev, ld, ld, 0};
     float* Pt = P + (int64_t)(d - 1 - t) * Zh * h * h;
     { ProfScope ps(WD_PROF_DW);
-    if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh)));
+    if (have_S) {   // the forward pass left S_t in the workspace: a plain TMA-fed contraction
+      AOperand ys{L.p(ws, L.S) + (int64_t)(t - 1) * L.szB, nullptr, nullptr, nullptr, ld, 0, 0};
+      WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s, dZ, ld, ys, h, 0, Pt, Nb, h, Zh)));
+    } else if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh)));
     else      WD_TRY((dw_partial<A_GATHER_DIFF, ACT, false>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh))); }
     // dS = dZ_t * W_h ; dA[a] = sum over out-edges of a of dS  (transpose-CSR, no atomics)
     AOperand a_z{dZ, nullptr, nullptr, nullptr, ld, 0, 0};

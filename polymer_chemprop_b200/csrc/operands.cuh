@@ -21,6 +21,8 @@ struct AOperand {
   const int32_t* src;  // GATHER_DIFF: b2a
   const int32_t* rev;  // GATHER_DIFF: b2revb
   int ldx, ldx2, K1;
+  float* S_out;        // GATHER_DIFF on the tensor-core path: the operand rows X[src] - act?(X2[rev]) are also
+                       // written here ([M, ldx2], fp32) so that the weight-gradient pass can read them as a plain matrix
 };
 
 template <int AMODE, int ACT, bool PREACT>

@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
                                 nullptr, nullptr, 0, Pz, p.ldp);
   }
 #ifdef WD_T2_TIMING
-  if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
+  if (WD_TIMING_ON(13) && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
     if (warp == 0 || warp == T2_MMA_WARP || warp == 6 || warp == D3_XFORM_W0)
       for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
     if (warp == 0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));

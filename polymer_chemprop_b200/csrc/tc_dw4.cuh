@@ -272,7 +272,7 @@ __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
     }
   }
 #ifdef WD_T2_TIMING
-  if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
+  if (WD_TIMING_ON(14) && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
     if (warp == D4_MMA_WARP || warp == D4_LOAD_W0 || warp == D4_XFORM_W0)
       for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
     if (warp == D4_XFORM_W0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));

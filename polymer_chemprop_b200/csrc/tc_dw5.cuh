@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_con
     }
   }
 #ifdef WD_T2_TIMING
-  if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
+  if (WD_TIMING_ON(15) && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
     if (warp == D5_MMA_WARP || warp == D5_TMA_WARP || warp == D5_LOAD_W0 || warp == D5_XFORM_W0)
       for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
     if (warp == D5_LOAD_W0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));

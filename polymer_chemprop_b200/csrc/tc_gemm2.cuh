@@ -48,6 +48,10 @@ constexpr int T2_OP_STAGES = 2;                   // operand rings (A swizzled, 
 //  0 xform<-raw_full 1 xform<-a_empty 2 loader<-raw_empty 3 bload<-b_empty 4 mma<-tmem_empty 5 mma<-a_full
 //  6 mma<-b_full 7 epi<-tmem_full 8 epi<-r_full 9 rload<-r_empty 15 kernel cycles
 __device__ unsigned long long g_t2_timing[16];
+#ifndef WD_T2_TIMING_ONLY
+#define WD_T2_TIMING_ONLY 0          // 0: every instrumented kernel records; n: only kernel generation n (2, 3, 4 gemm; 14, 15 dW)
+#endif
+#define WD_TIMING_ON(n) (WD_T2_TIMING_ONLY == 0 || WD_T2_TIMING_ONLY == (n))
 #ifdef WD_T2_TIMING
 #define T2_WAIT(slot, b, par) do { const long long t0_ = clock64(); ptx::mbar_wait(b, par); tacc[slot] += clock64() - t0_; } while (0)
 #else
@@ -151,6 +155,8 @@ struct T2Params {
   int ldc;
   int64_t M;
   int N, BN, n_tiles;
+  float* S;             // optional copy of the virtual A operand (segment 0, before rounding), [M, lds]
+  int lds;
 };
 
 template <int NSRC, int EPI, int ACT, bool PREACT>
@@ -228,6 +234,9 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
     const int t = threadIdx.x - T2_XFORM_T0, c = t & 7, rb = t >> 3;     // rows rb + T2_XR * j
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      // the first column tile of every row tile also writes the operand rows out (read back by the dW pass)
+      const int64_t srow0 = (tile / p.n_tiles) * TC_BM;
+      const bool keep = p.S != nullptr && (tile % p.n_tiles) == 0;
       for (int kc = 0; kc < p.KC; ++kc, ++it) {
         const int s = it % SR, as = it % T2_OP_STAGES;
         T2_WAIT(0, &bar->raw_full[s], (it / SR) & 1);
@@ -256,6 +265,8 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
               v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
             }
             if (dead) v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (keep && kc * TC_BK + c * 4 < p.lds && srow0 + rb + T2_XR * (j0 + j) < p.M)
+              *reinterpret_cast<float4*>(p.S + (srow0 + rb + T2_XR * (j0 + j)) * p.lds + kc * TC_BK + c * 4) = v[j];
             tc_store_piece(oa, rb + T2_XR * (j0 + j), c, v[j]);
           }
         }
@@ -409,7 +420,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
     }
   }
 #ifdef WD_T2_TIMING
-  if (blockIdx.x == 0 && lane == 0) {
+  if (WD_TIMING_ON(2) && blockIdx.x == 0 && lane == 0) {
     if (warp == 0 || warp == T2_MMA_WARP || warp == T2_BLOAD_WARP || warp == 6 || warp == 6 + T2_LOAD_WARPS || warp == T2_RLOAD_WARP)
       for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
     if (warp == 0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));

@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
     }
   }
 #ifdef WD_T2_TIMING
-  if (blockIdx.x == 0 && lane == 0) {
+  if (WD_TIMING_ON(3) && blockIdx.x == 0 && lane == 0) {
     if (warp == 0 || warp == T2_MMA_WARP || warp == T3_PROD_WARP)
       for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
     if (warp == 0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));

@@ -1,0 +1,344 @@
+// tcgen05 contraction kernel for the GATHERED depth step, fourth generation:
+//
+//   C[M, ldc] = act( R + (X0[i0(r), :] - act?(X1[i1(r), :])) * B^T + bias )       (mpn.py:119-123 as one kernel)
+//
+// Measured on the second generation (profiles/r1_g_*): cp.async (LDGSTS) moves ~12 bytes / cycle / SM and is the
+// binding limit; with two column tiles of 160 every gathered row was fetched twice, and the residual tile
+// went through LDGSTS as well.  Here
+//   * one CTA tile spans up to 304 output columns (two accumulator halves of <= 160), so each gathered row is
+//     fetched ONCE; three 160-column TMEM buffers rotate (tile i: buffers 2i, 2i+1 mod 3), the epilogue of
+//     tile i overlaps the main loop of tile i+1;
+//   * loaders cp.async the two gathered sources straight to their SWIZZLE_128B positions; the transform warps
+//     subtract / activate / round to TF32 IN PLACE (no second operand ring) and, for the first column tile,
+//     write the operand rows S out for the weight-gradient pass (after the hand-off to the MMA);
+//   * the residual tile arrives by TMA (FLOAT32 map, SWIZZLE_128B) in a ring that doubles as the epilogue's
+//     transpose staging; the packed weight chunk [BN x 128 B] by bulk copy.
+//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 gather loaders, 11-14 transform.
+#pragma once
+#include "tc_gemm3.cuh"
+
+namespace wd {
+
+constexpr int T4_MMA_WARP = 4, T4_B_WARP = 5, T4_R_WARP = 6, T4_LOAD_W0 = 7, T4_LOAD_WARPS = 4, T4_XFORM_W0 = 11,
+              T4_XFORM_WARPS = 4;
+constexpr int T4_THREADS = 32 * (T4_XFORM_W0 + T4_XFORM_WARPS);
+constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_R_SLOTS = 3;
+constexpr int T4_A_STAGE = 2 * TC_A_STAGE;        // two gathered sources, 128 rows x 128 bytes each
+constexpr int T4_R_SLOT = TC_BM * 128;            // residual / staging slot: 128 rows x 32 floats, swizzled
+constexpr int T4_HALF = 160, T4_MAX_BN = 304;     // accumulator half / widest column tile
+static_assert(T4_LOAD_WARPS * 32 == TC_BM && T4_XFORM_WARPS * 32 == TC_BM, "8 threads per row, 16 rows per pass");
+
+struct T4Barriers {
+  uint64_t raw_full[T4_A_STAGES], op_full[T4_A_STAGES], a_empty[T4_A_STAGES];
+  uint64_t b_full[T4_B_STAGES], b_empty[T4_B_STAGES];
+  uint64_t r_full[T4_R_SLOTS], r_empty[T4_R_SLOTS];
+  uint64_t tmem_full[3], tmem_empty[3];
+  uint32_t tmem_base;
+};
+
+struct T4Params {
+  CUtensorMap mr;       // residual R[M, N] (FLOAT32, box 128 x 32, SWIZZLE_128B)
+  const float* X0;      // minuend rows   (row map i0)
+  const float* X1;      // subtrahend rows (row map i1)
+  const int32_t* i0;
+  const int32_t* i1;
+  int ld0, ld1, K, KC;
+  const float* Bp;      // packed weights, images of [BN x 128 bytes] per (column tile, K chunk)
+  const float* bias;
+  float* C;
+  int ldc;
+  int64_t M;
+  int N, BN, n_tiles;
+  float* S;             // optional copy of the operand rows, [M, lds]
+  int lds;
+};
+
+inline int t4_smem_bytes(int BN) {
+  return 1024 + T4_A_STAGES * T4_A_STAGE + T4_B_STAGES * BN * 128 + T4_R_SLOTS * T4_R_SLOT + (int)sizeof(T4Barriers) + 64;
+}
+
+// Epilogue of one accumulator half (128 rows x W columns), 32 columns at a time: the row-owning thread adds its
+// accumulator row to the residual chunk in the (swizzled) ring slot, then the warp writes the 32 rows out with
+// 16-byte stores (8 lanes per row), applying bias + activation.
+template <int ACT>
+__device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T4Barriers* bar,
+                                            uint32_t& rit, int W, int64_t row0, int64_t M, int col0, int N, int cmax,
+                                            const float* bias, float* C, int ldc, long long* tacc) {
+  for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
+    const int slot = rit % T4_R_SLOTS;
+    uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
+    float v[32];
+    const uint32_t ta = tmem_acc + ((uint32_t)(we * 32) << 16) + (uint32_t)c0;
+    if (W - c0 >= 32) {
+      ptx::tmem_ld32(ta, v);
+    } else {
+      ptx::tmem_ld16(ta, v);
+#pragma unroll
+      for (int j = 16; j < 32; ++j) v[j] = 0.f;
+    }
+    T2_WAIT(8, &bar->r_full[slot], (rit / T4_R_SLOTS) & 1);
+    ptx::tmem_ld_wait();
+    uint8_t* myrow = sl + lane * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float4* q = reinterpret_cast<float4*>(myrow + ((j ^ (lane & 7)) << 4));
+      const float4 r = *q;
+      *q = make_float4(v[4 * j] + r.x, v[4 * j + 1] + r.y, v[4 * j + 2] + r.z, v[4 * j + 3] + r.w);
+    }
+    __syncwarp();
+    const int pc = lane & 7, rq = lane >> 3;
+    const int colb = col0 + c0 + pc * 4;
+    const int nval = (c0 + pc * 4 < W) ? max(0, min(4, N - colb)) : 0;
+    const bool in_c = colb < cmax && c0 + pc * 4 < W;
+    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (bias != nullptr) {
+      if (nval > 0) bv.x = __ldg(bias + colb);
+      if (nval > 1) bv.y = __ldg(bias + colb + 1);
+      if (nval > 2) bv.z = __ldg(bias + colb + 2);
+      if (nval > 3) bv.w = __ldg(bias + colb + 3);
+    }
+    float4 xv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int rr = rq + 4 * i;
+      xv[i] = *reinterpret_cast<const float4*>(sl + rr * 128 + ((pc ^ (rr & 7)) << 4));
+    }
+    float* cp = C + (row0 + we * 32 + rq) * ldc + colb;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
+      x = f4_act<ACT>(x);
+      if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
+      if (in_c && row0 + we * 32 + rq + 4 * i < M) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
+    }
+    ptx::fence_proxy_async_smem();            // generic accesses of the slot are ordered before the next TMA write
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
+  }
+}
+
+template <int ACT, bool PREACT>
+__global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constant__ T4Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = ptx::smem_u32(smem_raw);
+  uint8_t* ringA = smem_raw + (((base + 1023u) & ~1023u) - base);      // 1024-aligned
+  const int b_stage = p.BN * 128;
+  uint8_t* ringB = ringA + T4_A_STAGES * T4_A_STAGE;
+  uint8_t* rring = ringB + T4_B_STAGES * b_stage;
+  T4Barriers* bar = reinterpret_cast<T4Barriers*>(rring + T4_R_SLOTS * T4_R_SLOT);
+  long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  const long long t_start = clock64();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < T4_A_STAGES; ++s) {
+      ptx::mbar_init(&bar->raw_full[s], 32 * T4_LOAD_WARPS);
+      ptx::mbar_init(&bar->op_full[s], T4_XFORM_WARPS);
+      ptx::mbar_init(&bar->a_empty[s], 1);
+    }
+    for (int s = 0; s < T4_B_STAGES; ++s) { ptx::mbar_init(&bar->b_full[s], 1); ptx::mbar_init(&bar->b_empty[s], 1); }
+    for (int s = 0; s < T4_R_SLOTS; ++s) { ptx::mbar_init(&bar->r_full[s], 1); ptx::mbar_init(&bar->r_empty[s], T2_EPI_WARPS); }
+    for (int a = 0; a < 3; ++a) { ptx::mbar_init(&bar->tmem_full[a], 1); ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS); }
+    ptx::fence_barrier_init();
+    ptx::tma_prefetch_desc(&p.mr);
+  }
+  if (warp == T4_MMA_WARP) ptx::tmem_alloc(&bar->tmem_base, TC_TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = bar->tmem_base;
+  const int64_t total = ceil_div(p.M, TC_BM) * p.n_tiles;
+  const int W0 = min(p.BN, T4_HALF), W1 = p.BN - W0;                  // accumulator halves of a column tile
+
+  if (warp >= T4_XFORM_W0) {
+    // ================= transform, in place: X0 <- tf32(X0 - act?(X1)) =================
+    // (Fetching the subtrahend rows with plain loads into registers instead was measured SLOWER: the proxy fence
+    //  below is a MEMBAR that also waits for the thread's outstanding global loads, i.e. for the prefetch.)
+    const int t = threadIdx.x - 32 * T4_XFORM_W0, c = t & 7, rb = t >> 3;
+    const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));   // rows rb + 16 j share rb & 7
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+      const bool keep = p.S != nullptr && (tile % p.n_tiles) == 0;
+      for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        const int s = it % T4_A_STAGES;
+        T2_WAIT(0, &bar->raw_full[s], (it / T4_A_STAGES) & 1);
+        uint8_t* st = ringA + s * T4_A_STAGE + po;
+        float4 v[8], u[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          v[j] = *reinterpret_cast<const float4*>(st + j * 2048);
+          u[j] = *reinterpret_cast<const float4*>(st + TC_A_STAGE + j * 2048);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (PREACT) u[j] = f4_act<ACT>(u[j]);
+          v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
+          *reinterpret_cast<float4*>(st + j * 2048) =
+              make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
+        }
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->op_full[s]);
+        const int kcol = kc * TC_BK + c * 4;                             // S goes out after the hand-off to the MMA
+        if (keep && kcol < p.lds) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int64_t r = row0 + rb + 16 * j;
+            if (r < p.M) *reinterpret_cast<float4*>(p.S + r * p.lds + kcol) = v[j];
+          }
+        }
+      }
+    }
+  } else if (warp >= T4_LOAD_W0) {
+    // ================= gather loaders: cp.async, 8 threads per row, rows rb + 16 j =================
+    const int t = threadIdx.x - 32 * T4_LOAD_W0, c = t & 7, rb = t >> 3;
+    const uint32_t ring_u32 = ptx::smem_u32(ringA);
+    const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+      const float* s0[8];
+      const float* s1[8];
+      uint32_t okmask = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int64_t r = row0 + rb + 16 * j;
+        const bool ok = r < p.M;
+        okmask |= (ok ? 1u : 0u) << j;
+        int64_t a = ok ? r : 0, b = a;
+        if (ok && p.i0) a = __ldg(p.i0 + r);
+        if (ok && p.i1) b = __ldg(p.i1 + r);
+        s0[j] = p.X0 + a * p.ld0 + c * 4;
+        s1[j] = p.X1 + b * p.ld1 + c * 4;
+      }
+      for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        const int s = it % T4_A_STAGES;
+        T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+        const int k = kc * TC_BK + c * 4;
+        const int rem = (p.K - k) * 4;
+        const uint32_t valid = rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u);
+        const uint32_t d0 = ring_u32 + s * T4_A_STAGE + po;
+        if (okmask == 0xFFu && valid == 16u) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            ptx::cp_async16(d0 + j * 2048, s0[j] + kc * TC_BK, 16u);
+            ptx::cp_async16(d0 + j * 2048 + TC_A_STAGE, s1[j] + kc * TC_BK, 16u);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t v = ((okmask >> j) & 1u) ? valid : 0u;
+            ptx::cp_async16(d0 + j * 2048, v ? s0[j] + kc * TC_BK : p.X0, v);
+            ptx::cp_async16(d0 + j * 2048 + TC_A_STAGE, v ? s1[j] + kc * TC_BK : p.X1, v);
+          }
+        }
+        ptx::cp_async_arrive(&bar->raw_full[s]);
+      }
+    }
+  } else if (warp == T4_R_WARP) {
+    // ================= residual loader: TMA boxes of 128 rows x 32 columns, ahead of the epilogue =================
+    if (lane == 0) {
+      uint32_t rit = 0;
+      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int row0 = (int)((tile / p.n_tiles) * TC_BM);
+        const int col0 = (int)(tile % p.n_tiles) * p.BN;
+        for (int c0 = 0; c0 < p.BN; c0 += 32, ++rit) {
+          // the halves are walked in order: columns [0, W0) then [W0, BN); W0 is a multiple of 32 whenever W1 > 0
+          const int slot = rit % T4_R_SLOTS;
+          T2_WAIT(9, &bar->r_empty[slot], ((rit / T4_R_SLOTS) & 1) ^ 1);
+          ptx::mbar_arrive_expect_tx(&bar->r_full[slot], (uint32_t)T4_R_SLOT);
+          ptx::tma_load_2d(rring + slot * T4_R_SLOT, &p.mr, col0 + c0, row0, &bar->r_full[slot]);
+        }
+      }
+    }
+  } else if (warp == T4_B_WARP) {
+    // ================= weight loader: one bulk copy per K chunk =================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int nt = (int)(tile % p.n_tiles);
+        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+          const int bs = it % T4_B_STAGES;
+          T2_WAIT(3, &bar->b_empty[bs], ((it / T4_B_STAGES) & 1) ^ 1);
+          ptx::mbar_arrive_expect_tx(&bar->b_full[bs], (uint32_t)b_stage);
+          ptx::bulk_g2s(ringB + bs * b_stage, p.Bp + ((int64_t)nt * p.KC + kc) * p.BN * 32, (uint32_t)b_stage, &bar->b_full[bs]);
+        }
+      }
+    }
+  } else if (warp == T4_MMA_WARP) {
+    // ================= MMA issue: two accumulator halves per tile, three rotating TMEM buffers =================
+    uint32_t it = 0, g = 0;                                              // g: accumulator halves issued so far
+    const uint32_t id0 = ptx::idesc_tf32(128, W0), id1 = ptx::idesc_tf32(128, W1 > 0 ? W1 : 16);
+    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const uint32_t g0 = g, g1 = g + 1;
+      g += W1 > 0 ? 2 : 1;
+      for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        const int s = it % T4_A_STAGES, bs = it % T4_B_STAGES;
+        T2_WAIT(5, &bar->op_full[s], (it / T4_A_STAGES) & 1);
+        T2_WAIT(6, &bar->b_full[bs], (it / T4_B_STAGES) & 1);
+        const uint32_t a_addr = ptx::smem_u32(ringA + s * T4_A_STAGE), b_addr = ptx::smem_u32(ringB + bs * b_stage);
+        if (kc == 0) T2_WAIT(4, &bar->tmem_empty[g0 % 3], ((g0 / 3) & 1) ^ 1);
+        ptx::tc_fence_after();
+        if (lane == 0) {
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks)
+            ptx::mma_tf32(tmem_base + (g0 % 3) * T4_HALF, ptx::smem_desc_sw128(a_addr + ks * 32),
+                          ptx::smem_desc_sw128(b_addr + ks * 32), id0, (kc == 0 && ks == 0) ? 0u : 1u);
+        }
+        if (W1 > 0) {
+          if (kc == 0) { T2_WAIT(4, &bar->tmem_empty[g1 % 3], ((g1 / 3) & 1) ^ 1); ptx::tc_fence_after(); }
+          if (lane == 0) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+              ptx::mma_tf32(tmem_base + (g1 % 3) * T4_HALF, ptx::smem_desc_sw128(a_addr + ks * 32),
+                            ptx::smem_desc_sw128(b_addr + W0 * 128 + ks * 32), id1, (kc == 0 && ks == 0) ? 0u : 1u);
+          }
+        }
+        if (lane == 0) {
+          ptx::tc_commit(&bar->a_empty[s]);
+          ptx::tc_commit(&bar->b_empty[bs]);
+          if (kc == p.KC - 1) {
+            ptx::tc_commit(&bar->tmem_full[g0 % 3]);
+            if (W1 > 0) ptx::tc_commit(&bar->tmem_full[g1 % 3]);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ================= epilogue (warps 0-3) =================
+    uint32_t g = 0, rit = 0;
+    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+      const int col0 = (int)(tile % p.n_tiles) * p.BN;
+      for (int hb = 0; hb < (W1 > 0 ? 2 : 1); ++hb, ++g) {
+        const int buf = g % 3;
+        T2_WAIT(7, &bar->tmem_full[buf], (g / 3) & 1);
+        ptx::tc_fence_after();
+        t4_epilogue<ACT>(tmem_base + buf * T4_HALF, warp, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
+                         col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc);
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[buf]);
+      }
+    }
+  }
+#ifdef WD_T2_TIMING
+  if (WD_TIMING_ON(4) && blockIdx.x == 0 && lane == 0) {
+    if (warp == 0 || warp == T4_MMA_WARP || warp == T4_B_WARP || warp == T4_R_WARP || warp == T4_LOAD_W0 || warp == T4_XFORM_W0)
+      for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
+    if (warp == 0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));
+  }
+#else
+  (void)tacc; (void)t_start;
+#endif
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == T4_MMA_WARP) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
+  }
+}
+
+}  // namespace wd

@@ -1,6 +1,7 @@
 // Host-side launch helpers of the tcgen05 contraction kernels (tc_gemm.cuh / tc_dw.cuh).
 #pragma once
 #include "tc_gemm3.cuh"
+#include "tc_gemm4.cuh"
 #include "tc_dw.cuh"
 #include "tc_dw2.cuh"
 #include "tc_dw3.cuh"
@@ -27,11 +28,17 @@ inline int tc_dw_version() {   // WD_TC_DW=1..5: generation of the dW kernel (de
   return tc_use_v1() ? 1 : v;
 }
 
-inline TcPacked tc_packed_geometry(int N, int K1, int K2) {
+inline bool tc_use_gemm4() {   // WD_TC_GEMM4=0 keeps the gathered depth step on the second-generation kernel
+  static bool v = [] { const char* e = getenv("WD_TC_GEMM4"); return !(e && atoi(e) == 0); }();
+  return v && !tc_use_v1();
+}
+
+// max_bn: widest column tile the consuming kernel takes (160: two TMEM accumulators; 304: the gathered kernel)
+inline TcPacked tc_packed_geometry(int N, int K1, int K2, int max_bn = T2_MAX_BN) {
   TcTiling t = tc_tiling(N);
-  if (!tc_use_v1() && t.BN > T2_MAX_BN) {     // second generation: two accumulators must fit TMEM
+  if (!tc_use_v1() && t.BN > max_bn) {
     const int np = (int)round_up(N, 16);
-    t.n_tiles = (int)ceil_div(np, std::min(tc_max_bn(), T2_MAX_BN));
+    t.n_tiles = (int)ceil_div(np, std::min(tc_max_bn(), max_bn));
     t.BN = (int)round_up(ceil_div(np, t.n_tiles), 16);
   }
   TcPacked g{N, K1, K2, t.BN, t.n_tiles, (int)ceil_div(K1, TC_BK), 0, nullptr};
@@ -62,6 +69,7 @@ int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   constexpr int NSRC = AMODE == A_GATHER_DIFF ? 2 : 1;
   if (AMODE == A_GATHER_DIFF) {
     p.seg[0] = T2Seg{A.X, A.X2, A.src, A.rev, A.ldx, A.ldx2, B.K1, 1};
+    p.S = A.S_out; p.lds = A.ldx2;
     if (!tc_aligned16(A.X, A.ldx) || !tc_aligned16(A.X2, A.ldx2))
       return fail(WD_ERR_INVALID_ARG, "tcgen05 gather operand needs 16-byte aligned rows");
   } else {
@@ -81,6 +89,31 @@ int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   const int64_t tiles = ceil_div(M, TC_BM) * B.n_tiles;
   const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
   WD_LAUNCH(kern, grid, T2_THREADS, smem, s, p);
+  return WD_OK;
+}
+
+// fourth-generation kernel for the gathered depth step (column tiles up to 304 wide, in-place transform, TMA residual)
+template <int ACT, bool PREACT>
+int tc_gemm4(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
+             float* C, int ldc, int64_t M) {
+  T4Params p{};
+  if (!tc_aligned16(A.X, A.ldx) || !tc_aligned16(A.X2, A.ldx2) || !tc_aligned16(R, ldr) || !tc_aligned16(C, ldc))
+    return fail(WD_ERR_INVALID_ARG, "tcgen05 gathered step needs 16-byte aligned rows");
+  if (B.BN > T4_MAX_BN || B.K2 != 0) return fail(WD_ERR_UNSUPPORTED, "tcgen05 gathered step: unsupported tile geometry");
+  int rc = tma_make_2d(&p.mr, R, M, B.N, ldr, TC_BM, TMA_SW128, /*round_tf32=*/false);
+  if (rc != WD_OK) return rc;
+  p.X0 = A.X; p.X1 = A.X2; p.i0 = A.src; p.i1 = A.rev; p.ld0 = A.ldx; p.ld1 = A.ldx2; p.K = B.K1; p.KC = B.KC;
+  p.Bp = B.img; p.bias = bias; p.C = C; p.ldc = ldc; p.M = M;
+  p.N = B.N; p.BN = B.BN; p.n_tiles = B.n_tiles;
+  p.S = A.S_out; p.lds = A.ldx2;
+  const int smem = t4_smem_bytes(B.BN);
+  if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 tile does not fit shared memory");
+  auto kern = k_tc_gemm4<ACT, PREACT>;
+  rc = tc_set_smem(kern, smem);
+  if (rc != WD_OK) return rc;
+  const int64_t tiles = ceil_div(M, TC_BM) * B.n_tiles;
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
+  WD_LAUNCH(kern, grid, T4_THREADS, smem, s, p);
   return WD_OK;
 }
 
@@ -141,6 +174,7 @@ template <int AMODE, int EPI, int ACT, bool PREACT>
 int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
             float* C, int ldc, int64_t M) {
   if (!tc_use_v1()) {
+    if (AMODE == A_GATHER_DIFF && EPI == E_RES_ACT && B.BN > T2_MAX_BN) return tc_gemm4<ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M);
     using D3 = TcGemm3Dispatch<AMODE, EPI, ACT, PREACT>;
     if (D3::ok && tc_use_gemm3() && B.BN <= T2_MAX_BN && tc_aligned16(A.X, A.ldx) && tc_aligned16(C, ldc) &&
         (AMODE != A_CONCAT || tc_aligned16(A.X2, A.ldx2)))

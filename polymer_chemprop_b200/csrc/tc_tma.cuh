@@ -30,14 +30,15 @@ enum TmaSwizzle { TMA_SW128 = 0, TMA_SW128_ATOM32 = 1 };
 
 // Map over X[rows, cols] (row stride ld floats; base and rows 16-byte aligned), box = box_rows x 32 columns.
 // Elements outside [rows, cols] read as zero.
-inline int tma_make_2d(CUtensorMap* map, const float* X, int64_t rows, int cols, int ld, int box_rows, TmaSwizzle sw) {
+inline int tma_make_2d(CUtensorMap* map, const float* X, int64_t rows, int cols, int ld, int box_rows, TmaSwizzle sw,
+                       bool round_tf32 = true) {
   PFN_wdEncodeTiled enc = tma_encode_fn();
   if (!enc) return fail(WD_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
   const cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1u, 1u};
-  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 2, const_cast<float*>(X), dims, strides, box, estr,
+  const CUresult r = enc(map, round_tf32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(X), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE,
                          sw == TMA_SW128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

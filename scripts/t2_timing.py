@@ -59,7 +59,35 @@ def run_dw(Rn, N1, N2):
         print(f"   {n:20s} {100.0 * buf[i] / tot:6.1f}% of kernel")
 
 
+def run_encoder():
+    """Wait-cycle counters of whatever instrumented kernels one encoder forward + backward launches (build the
+    timing library with -DWD_T2_TIMING_ONLY=n to isolate one kernel generation, e.g. 4 = gathered depth step)."""
+    import types
+    from polymer_chemprop_b200 import MPN, BatchMolGraph, synth
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 4096, seed=0))
+    args = types.SimpleNamespace(
+        hidden_size=300, depth=3, bias=False, dropout=0.0, activation="ReLU", atom_messages=False, undirected=False,
+        aggregation="mean", aggregation_norm=100, atom_descriptors=None, atom_descriptors_size=0, device=DEV,
+        mpn_shared=False, number_of_molecules=1, features_only=False, use_input_features=False,
+        overwrite_default_atom_features=False, overwrite_default_bond_features=False, wd_math_mode="tf32")
+    model = MPN(args, atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)
+    buf = (C.c_uint64 * 16)()
+    for it in range(2):
+        L.wd_debug_timing(buf, 1)
+        out = model([bmg])
+        out.sum().backward()
+        torch.cuda.synchronize()
+    L.wd_debug_timing(buf, 0)
+    tot = buf[15] or 1
+    print(f"encoder fwd+bwd, CTA0 cycles of the instrumented kernels {tot}")
+    for i, n in enumerate(NAMES):
+        print(f"   {n:20s} {100.0 * buf[i] / tot:6.1f}% of kernel")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "encoder":
+        run_encoder()
+        sys.exit(0)
     run_dw(269541, 300, 300)
     run_dw(269541, 300, 147)
     run(269541, 300, 300, 0)
