@@ -180,18 +180,26 @@ class ClockSampler:
 # algorithmic bytes per launch of each kernel category (DESIGN.md "Kernels and rooflines")
 # --------------------------------------------------------------------------------------------
 def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d):
+    """Compulsory HBM bytes per launch of each kernel category (average over the launches of the category in one
+    step), for the algorithm as implemented: S_t is written by the forward depth steps and read back by dW_h."""
     P, Q = 4.0 * Nb * h, 4.0 * Na * h            # one [N_b,h] / [N_a,h] fp32 pass
     steps = max(d - 1, 1)
-    depth_total = (2 * P + Q) + (d - 2) * (3 * P + Q) if d > 1 else 0.0   # t=1 reads I once
+    depth_total = ((3 * P + Q) + (d - 2) * (4 * P + Q)) if d > 1 else 0.0    # t=1 reads I once; every step writes S_t
+    if d > 1:
+        msg_total = (2 * P + Q) + (d - 2) * (5 * P + Q) + (4 * P + Q)         # first / middle / last step
+    else:
+        msg_total = 2 * P + Q
+    dw_total = (2 * Q + 4.0 * Na * Fa) + (d - 1) * 2 * P + (P + 4.0 * Nb * Fb)   # dW_o, dW_h x (d-1), dW_i
+    dx_total = 2 * Q + (d - 1) * 2 * P                                          # dA_d, dS x (d-1)
     return {
         "input_proj": 4.0 * Nb * Fb + P + 4.0 * h * Fb,
         "aggregate": P + Q + 12.0 * Nb + 4.0 * Na,
         "depth_step": depth_total / steps + 8.0 * Nb + 4.0 * h * h,
         "atom_update": 4.0 * Na * Fa + 2 * Q + 4.0 * h * (Fa + h),
         "readout": (2 * Q + 4.0 * G * h) * 0.5 + (Q + 4.0 * G * h) * 0.5,   # bwd (H, dZo, d_out) / fwd (H, out)
-        "msg_grad": 4 * P + Q + 12.0 * Nb,        # dS, Y, dZ, dI + gathered dA rows
-        "dw": 2 * P,                              # dZ and the recomputed S / features (per dW launch)
-        "dx": 2 * P + 4.0 * h * h,
+        "msg_grad": msg_total / d + 12.0 * Nb,
+        "dw": dw_total / (d + 1),
+        "dx": dx_total / d + 4.0 * h * h,
         "scatter": P + Q + 8.0 * Nb,
         "misc": 0.0,
         "reduce": 0.0,

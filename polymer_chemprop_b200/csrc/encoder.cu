@@ -18,7 +18,7 @@ namespace {
 struct Layout {
   int ldh;                 // row stride of every [*, h] activation buffer (h rounded up to 4)
   int64_t szB, szA;        // floats per [N_b, ldh] / [N_a, ldh] buffer
-  int64_t I, M, Agg, H, mscale, U, dZ, dS, dI, dA, dZo, partials, total;
+  int64_t I, M, Agg, H, mscale, U, dZ, dZ2, dS, dI, dA, dZo, partials, total;
   int64_t S;               // TF32 mode: S_t = A_t[b2a] - M_{t-1}[b2revb] written by the forward depth steps, read by dW_h
   int Z;                   // max row chunks of the weight-gradient contractions (sizes `partials`)
   int Zh, Zi, Zo;          // row chunks of the dW_h / dW_i / dW_o contractions
@@ -52,6 +52,7 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   L.U = take(c.undirected ? L.szB : 0);
   L.S = take(c.math_mode == WD_MATH_TF32 ? (int64_t)std::max(0, c.depth - 1) * L.szB : 0);
   L.dZ = take(L.szB);
+  L.dZ2 = take(c.depth > 2 ? L.szB : 0);
   L.dS = take(L.szB);
   L.dI = take(L.szB);
   L.dA = take(L.szA);
@@ -227,18 +228,18 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
 }
 
 // ---- backward ---------------------------------------------------------------------------------
-template <int ACT, bool PREACT, bool HAS_DS, bool FIRST>
+template <int ACT, bool PREACT, bool HAS_DS, bool WRITE_DZ, bool WRITE_DI>
 int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const float* dA, const float* dS,
-                 const float* Y, int ld, float* dZ, float* dI) {
+                 const float* Y, int ld, float* dZ, const float* dI_in, float* dI) {
   const int nc4 = ld / 4;
   const int64_t Nb = g.n_bonds;
   ProfScope ps(WD_PROF_MSG_GRAD);
   if (c.undirected && HAS_DS)
-    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, FIRST>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
-              g.w_bonds, g.dst, g.rev, dZ, dI, Nb, nc4);
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
+              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4);
   else
-    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, FIRST>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
-              g.w_bonds, g.dst, g.rev, dZ, dI, Nb, nc4);
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
+              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4);
   return WD_OK;
 }
 
@@ -255,7 +256,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   }
   const int64_t Na = g.n_atoms, Nb = g.n_bonds;
   const int d = c.depth;
-  float *I = L.p(ws, L.I), *H = L.p(ws, L.H), *dZ = L.p(ws, L.dZ), *dS = L.p(ws, L.dS), *dI = L.p(ws, L.dI),
+  float *I = L.p(ws, L.I), *H = L.p(ws, L.H), *dS = L.p(ws, L.dS), *dI = L.p(ws, L.dI),
         *dA = L.p(ws, L.dA), *dZo = L.p(ws, L.dZo), *P = L.p(ws, L.partials);
   const int64_t pw = std::max<int64_t>((int64_t)std::max(1, d - 1) * h * h, (int64_t)h * std::max(Fo, Fb));
   float* Pcol = P + (int64_t)L.Z * pw;   // column-sum partials
@@ -279,14 +280,19 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_zo, w.W_o + Fa, Fo, nullptr, nullptr, 0, dA, ld, Na, h, h, &L.pWoT))); }
 
   const int Zh = L.Zh;
+  // dZ_t alternates between two buffers so that step t-1 can read dZ_t (as the running sum) while it writes its own;
+  // `sum` points at sum_{t' >= t} dZ_t': the first step's dZ itself (no separate dI write), dI afterwards
+  float* dZbuf[2] = {L.p(ws, L.dZ), L.p(ws, L.dZ2)};
+  const float* sum = nullptr;
   for (int t = d - 1; t >= 1; --t) {
+    float* dZ = dZbuf[(d - 1 - t) & 1];
     const float* M_t = L.p(ws, L.M) + (int64_t)(t - 1) * L.szB;
     const float* A_t = L.p(ws, L.Agg) + (int64_t)(t - 1) * L.szA;
     const float* M_prev = (t == 1) ? I : L.p(ws, L.M) + (int64_t)(t - 2) * L.szB;
     const bool pre = (t == 1);
     // dZ_t = dM_t * act'(M_t), dI += dZ_t ; dM_t = w_b dA[dst b] - dS[rev b] (symmetrised if undirected)
-    if (t == d - 1) WD_TRY((message_grad<ACT, false, false, true>(c, s, g, dA, dS, M_t, ld, dZ, dI)));
-    else            WD_TRY((message_grad<ACT, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, dI)));
+    if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI))); sum = dZ; }
+    else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI))); sum = dI; }
     // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
     const float* u = M_prev;
     bool upre = pre;
@@ -316,12 +322,12 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   if (d > 1) {
     { ProfScope ps(WD_PROF_DW);
     WD_TRY(reduce_partials(s, P, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
-    if (c.bias && gr.db_h) WD_TRY(colsum(s, dI, ld, Pcol, gr.db_h, Nb, h, Zh)); }  // dI == sum_{t>=1} dZ_t here
-    WD_TRY((message_grad<ACT, true, true, false>(c, s, g, dA, dS, I, ld, dZ, dI)));
+    if (c.bias && gr.db_h) WD_TRY(colsum(s, sum, ld, Pcol, gr.db_h, Nb, h, Zh)); }  // sum == sum_{t>=1} dZ_t here
+    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI)));
   } else {
     WD_CUDA_OK(cudaMemsetAsync(gr.dW_h, 0, sizeof(float) * h * h, s));
     if (c.bias && gr.db_h) WD_CUDA_OK(cudaMemsetAsync(gr.db_h, 0, sizeof(float) * h, s));
-    WD_TRY((message_grad<ACT, true, false, true>(c, s, g, dA, dS, I, ld, dZ, dI)));
+    WD_TRY((message_grad<ACT, true, false, false, true>(c, s, g, dA, dS, I, ld, nullptr, nullptr, dI)));
   }
   {  // dW_i = dI^T f_bonds ; db_i = colsum(dI)
     ProfScope ps(WD_PROF_DW);

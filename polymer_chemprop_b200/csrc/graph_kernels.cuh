@@ -46,12 +46,13 @@ __global__ void k_symmetrize(const float* __restrict__ X, int ld, const int32_t*
 //   g(b)  = w_b * dA[dst b] - dS[rev b]              (dS absent for the last step: HAS_DS = false)
 //   UNDIRECTED && HAS_DS:  g(b) = (g(b) + g(rev b)) / 2
 //   dZ[b] = g(b) * act'(Y[b])   with Y = M_t (PREACT: Y = act(I))
-//   dI[b] = (FIRST ? 0 : dI[b]) + dZ[b]
-template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool FIRST>
+//   dI[b] = (dI_in ? dI_in[b] : 0) + dZ[b]     (WRITE_DI; dI_in may alias dI or be the previous step's dZ)
+// WRITE_DZ = false for the last step (nothing reads dZ_0), WRITE_DI = false for the first one (dI == dZ then).
+template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool WRITE_DZ, bool WRITE_DI>
 __global__ void k_message_grad(const float* __restrict__ dA, const float* __restrict__ dS,
                                const float* __restrict__ Y, int ld, const float* __restrict__ w,
                                const int32_t* __restrict__ dst, const int32_t* __restrict__ rev,
-                               float* __restrict__ dZ, float* __restrict__ dI, int64_t n_rows, int nc4) {
+                               float* __restrict__ dZ, const float* dI_in, float* dI, int64_t n_rows, int nc4) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_rows * nc4) return;
   int64_t b = i / nc4;
@@ -75,12 +76,13 @@ __global__ void k_message_grad(const float* __restrict__ dA, const float* __rest
   if (PREACT) y = f4_act<ACT>(y);
   float4 dz = make_float4(g.x * act_bwd_from_out<ACT>(y.x), g.y * act_bwd_from_out<ACT>(y.y),
                           g.z * act_bwd_from_out<ACT>(y.z), g.w * act_bwd_from_out<ACT>(y.w));
-  st4(dZ + b * ld + c, dz);
-  if (FIRST) {
+  if (WRITE_DZ) st4(dZ + b * ld + c, dz);
+  if (WRITE_DI) {
+    if (dI_in != nullptr) {
+      const float4 di = *reinterpret_cast<const float4*>(dI_in + b * ld + c);
+      dz = make_float4(di.x + dz.x, di.y + dz.y, di.z + dz.z, di.w + dz.w);
+    }
     st4(dI + b * ld + c, dz);
-  } else {
-    float4 di = *reinterpret_cast<const float4*>(dI + b * ld + c);
-    st4(dI + b * ld + c, make_float4(di.x + dz.x, di.y + dz.y, di.z + dz.z, di.w + dz.w));
   }
 }
 
