@@ -206,6 +206,18 @@ def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d):
     }
 
 
+def measured_traffic(a, category):
+    """DRAM bytes per launch of `category` from the committed ncu capture (profiles/ncu_traffic.json), only for the
+    configuration that capture was taken on; None otherwise."""
+    if not (a.kind == "copolymer" and a.batch == 4096 and a.hidden == 300 and a.depth == 3 and a.math == "tf32"):
+        return None
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return t["bytes_per_launch"].get(category)
+    except Exception:
+        return None
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -368,7 +380,7 @@ def main():
                              "frac_of_hbm_peak": gbs / peak if gbs else None}
         dom = max((k for k in kernels if k not in ("misc", "reduce")), key=lambda k: kernels[k]["share_of_gpu_time"])
         roof = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
-                "unit": "GB/s", "frac": kernels[dom]["frac_of_hbm_peak"], "traffic": None,
+                "unit": "GB/s", "frac": kernels[dom]["frac_of_hbm_peak"], "traffic": measured_traffic(a, dom),
                 "peak_source": peak_src, "ms_per_launch": kernels[dom]["ms_per_launch"],
                 "alg_bytes_per_launch": alg[dom]}
         step_bytes = sum(alg[k] * v["launches_per_step"] for k, v in kernels.items())
