@@ -264,8 +264,12 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
 
   // readout + atom-update activation:  dZo = w_a * dop/den * d_out[mol] * act'(H)
   { ProfScope ps(WD_PROF_READOUT);
-  WD_LAUNCH((k_readout_grad<ACT>), grid1d(Na * ld), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
-            L.p(ws, L.mscale), dZo, Na); }
+  if (h % 4 == 0 && (reinterpret_cast<uintptr_t>(d_out) & 15) == 0)
+    WD_LAUNCH((k_readout_grad<ACT, true>), grid1d(Na * nc4), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
+              L.p(ws, L.mscale), dZo, Na);
+  else
+    WD_LAUNCH((k_readout_grad<ACT, false>), grid1d(Na * nc4), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
+              L.p(ws, L.mscale), dZo, Na); }
   {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zo;

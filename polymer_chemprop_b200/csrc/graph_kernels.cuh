@@ -20,11 +20,24 @@ __global__ void k_aggregate(const float* __restrict__ U, int ld, const float* __
   int c = (int)(i - a * nc4) * 4;
   int j0 = __ldg(ptr + a), j1 = __ldg(ptr + a + 1);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int j = j0; j < j1; ++j) {
-    int b = __ldg(idx + j);
-    float4 v = ldg4(U + (int64_t)b * ld + c);
-    if (PREACT) v = f4_act<ACT>(v);
-    acc = f4_fma(w ? __ldg(w + b) : 1.f, v, acc);
+  // four rows in flight per thread (lists hold ~3 entries): indices first, then the independent row loads;
+  // the accumulation order is the list order (the reference's order), missing slots add an exact 0
+  for (int j = j0; j < j1; j += 4) {
+    int b[4];
+    float wv[4];
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) b[u] = (j + u < j1) ? __ldg(idx + j + u) : -1;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      v[u] = b[u] >= 0 ? ldg4(U + (int64_t)b[u] * ld + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      wv[u] = b[u] >= 0 ? (w ? __ldg(w + b[u]) : 1.f) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (PREACT) v[u] = f4_act<ACT>(v[u]);
+      if (b[u] >= 0) acc = f4_fma(wv[u], v[u], acc);
+    }
   }
   st4(out + a * ld + c, acc);
 }
@@ -122,22 +135,37 @@ __global__ void k_readout(const float* __restrict__ H, int ld, const float* __re
 }
 
 // dZo[a, :] = w_atoms[a] * mscale[mol a] * d_out[mol a, :] * act'(H[a, :])   (0 for atoms in no scope)
-template <int ACT>
+template <int ACT, bool VEC4>
 __global__ void k_readout_grad(const float* __restrict__ d_out, int h, const float* __restrict__ H,
                                int ld, const float* __restrict__ w_atoms,
                                const int32_t* __restrict__ mol_of, const float* __restrict__ mscale,
                                float* __restrict__ dZo, int64_t n_atoms) {
+  const int nc4 = ld / 4;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_atoms * ld) return;
-  int64_t a = i / ld;
-  int c = (int)(i - a * ld);
+  if (i >= n_atoms * nc4) return;
+  int64_t a = i / nc4;
+  int c = (int)(i - a * nc4) * 4;
   int g = __ldg(mol_of + a);
-  float v = 0.f;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
   if (g >= 0 && c < h) {
-    float s = __ldg(w_atoms + a) * __ldg(mscale + g);
-    v = s * __ldg(d_out + (int64_t)g * h + c) * act_bwd_from_out<ACT>(H[a * ld + c]);
+    const float s = __ldg(w_atoms + a) * __ldg(mscale + g);
+    const float4 y = *reinterpret_cast<const float4*>(H + a * ld + c);
+    const float* dp = d_out + (int64_t)g * h + c;
+    float4 d;
+    if (VEC4) {               // h % 4 == 0 and d_out 16-byte aligned
+      d = ldg4(dp);
+    } else {
+      d.x = __ldg(dp);
+      d.y = c + 1 < h ? __ldg(dp + 1) : 0.f;
+      d.z = c + 2 < h ? __ldg(dp + 2) : 0.f;
+      d.w = c + 3 < h ? __ldg(dp + 3) : 0.f;
+    }
+    v.x = s * d.x * act_bwd_from_out<ACT>(y.x);
+    v.y = c + 1 < h ? s * d.y * act_bwd_from_out<ACT>(y.y) : 0.f;
+    v.z = c + 2 < h ? s * d.z * act_bwd_from_out<ACT>(y.z) : 0.f;
+    v.w = c + 3 < h ? s * d.w * act_bwd_from_out<ACT>(y.w) : 0.f;
   }
-  dZo[a * ld + c] = v;
+  st4(dZo + a * ld + c, v);
 }
 
 }  // namespace wd

@@ -19,14 +19,18 @@
 
 namespace wd {
 
+#ifndef WD_T4_XFORM_WARPS
+#define WD_T4_XFORM_WARPS 4
+#endif
 constexpr int T4_MMA_WARP = 4, T4_B_WARP = 5, T4_R_WARP = 6, T4_LOAD_W0 = 7, T4_LOAD_WARPS = 4, T4_XFORM_W0 = 11,
-              T4_XFORM_WARPS = 4;
+              T4_XFORM_WARPS = WD_T4_XFORM_WARPS;
+constexpr int T4_XR = 4 * T4_XFORM_WARPS, T4_XJ = TC_BM / T4_XR;   // transform: rows per pass / passes per chunk
 constexpr int T4_THREADS = 32 * (T4_XFORM_W0 + T4_XFORM_WARPS);
 constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_R_SLOTS = 3;
 constexpr int T4_A_STAGE = 2 * TC_A_STAGE;        // two gathered sources, 128 rows x 128 bytes each
 constexpr int T4_R_SLOT = TC_BM * 128;            // residual / staging slot: 128 rows x 32 floats, swizzled
 constexpr int T4_HALF = 160, T4_MAX_BN = 304;     // accumulator half / widest column tile
-static_assert(T4_LOAD_WARPS * 32 == TC_BM && T4_XFORM_WARPS * 32 == TC_BM, "8 threads per row, 16 rows per pass");
+static_assert(T4_LOAD_WARPS * 32 == TC_BM && (T4_XFORM_WARPS == 4 || T4_XFORM_WARPS == 8), "8 threads per row");
 
 struct T4Barriers {
   uint64_t raw_full[T4_A_STAGES], op_full[T4_A_STAGES], a_empty[T4_A_STAGES];
@@ -155,7 +159,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     // (Fetching the subtrahend rows with plain loads into registers instead was measured SLOWER: the proxy fence
     //  below is a MEMBAR that also waits for the thread's outstanding global loads, i.e. for the prefetch.)
     const int t = threadIdx.x - 32 * T4_XFORM_W0, c = t & 7, rb = t >> 3;
-    const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));   // rows rb + 16 j share rb & 7
+    const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));   // rows rb + T4_XR j share rb & 7
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
       const int64_t row0 = (tile / p.n_tiles) * TC_BM;
@@ -164,17 +168,17 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         const int s = it % T4_A_STAGES;
         T2_WAIT(0, &bar->raw_full[s], (it / T4_A_STAGES) & 1);
         uint8_t* st = ringA + s * T4_A_STAGE + po;
-        float4 v[8], u[8];
+        float4 v[T4_XJ], u[T4_XJ];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          v[j] = *reinterpret_cast<const float4*>(st + j * 2048);
-          u[j] = *reinterpret_cast<const float4*>(st + TC_A_STAGE + j * 2048);
+        for (int j = 0; j < T4_XJ; ++j) {
+          v[j] = *reinterpret_cast<const float4*>(st + j * (T4_XR * 128));
+          u[j] = *reinterpret_cast<const float4*>(st + TC_A_STAGE + j * (T4_XR * 128));
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < T4_XJ; ++j) {
           if (PREACT) u[j] = f4_act<ACT>(u[j]);
           v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
-          *reinterpret_cast<float4*>(st + j * 2048) =
+          *reinterpret_cast<float4*>(st + j * (T4_XR * 128)) =
               make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
         }
         ptx::fence_proxy_async_smem();
@@ -183,8 +187,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         const int kcol = kc * TC_BK + c * 4;                             // S goes out after the hand-off to the MMA
         if (keep && kcol < p.lds) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int64_t r = row0 + rb + 16 * j;
+          for (int j = 0; j < T4_XJ; ++j) {
+            const int64_t r = row0 + rb + T4_XR * j;
             if (r < p.M) *reinterpret_cast<float4*>(p.S + r * p.lds + kcol) = v[j];
           }
         }
