@@ -69,8 +69,20 @@ def init_weights(model, seed=0):
 
 
 def workload_name(a):
+    if a.kind == "qm9":
+        cfg = "configs[2]: unweighted D-MPNN on QM9-shaped graphs"
+    elif a.hidden == 2400 and a.depth == 6:
+        cfg = "configs[3]: wide/deep, GEMM-dominated"
+    elif a.hidden == 300 and a.depth == 3:
+        cfg = "configs[1]" if world_size() == 1 else "configs[4]: data parallel, 4096 graphs per GPU"
+    else:
+        cfg = "not a BASELINE.json configuration"
     return (f"synthetic {a.kind}-shaped graphs, batch {a.batch}/GPU, hidden {a.hidden}, depth {a.depth} "
-            f"(BASELINE.json configs[1])")
+            f"(BASELINE.json {cfg})")
+
+
+def world_size():
+    return int(os.environ.get("WORLD_SIZE", "1"))
 
 
 # --------------------------------------------------------------------------------------------
