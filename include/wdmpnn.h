@@ -50,6 +50,10 @@ typedef struct WdConfig {
   int32_t bias;            /* args.bias: W_i / W_h carry a bias                  */
   int32_t math_mode;       /* WD_MATH_*                                          */
   float aggregation_norm;  /* args.aggregation_norm                              */
+  float dropout;           /* args.dropout p in [0,1) for THIS call: 0 in eval mode (nn.Dropout, mpn.py:38).  */
+  uint32_t dropout_seed_lo; /* Philox key of this call's masks; pass the SAME cfg to the backward call.        */
+  uint32_t dropout_seed_hi; /* The reference's RNG stream cannot be matched: masks are Philox4x32-10 words of  */
+                            /* (element index, site) -- restated in oracle/mpn_oracle.py for the parity tests.  */
 } WdConfig;
 
 /* One BatchMolGraph on the device: get_components() tensors (featurization.py:815-846) plus the
@@ -115,13 +119,34 @@ int wd_csr_build(const int64_t* a2b, int64_t n_atoms, int64_t max_num_bonds, con
 /* Synchronises `stream`, reads `flags` back and returns WD_ERR_GRAPH if flags[0] != 0. */
 int wd_csr_build_check(const int32_t* flags, void* stream);
 
+/* Rebuilds the get_components() feature matrices on the device from their compact form.  MolGraph
+ * builds every bond row as f_atoms[a1] + f_bond (featurization.py:467-468; polymer edges :616-629), so
+ * f_bonds[b, :F_a] == f_atoms[b2a[b]] and only the bond-only tail carries information:
+ *   f_bonds_out[b, :] = [ f_atoms[b2a[b], 0:atom_fdim], bond_tail[b, 0:tail_fdim], 0-pad to ld_bonds ]
+ *   f_atoms_out[a, :] = [ f_atoms[a, 0:atom_fdim], 0-pad to ld_atoms ]        (skipped if f_atoms_out == NULL)
+ * f_atoms [N_a, atom_fdim] and bond_tail [N_b, tail_fdim] are DENSE row-major device arrays, b2a the
+ * int64 device copy of BatchMolGraph.b2a; ld_* are multiples of 4 (WdGraph.ld_atoms / ld_bonds).
+ * Byte copies only: bit-identical to uploading f_bonds itself.  The caller is responsible for the
+ * prefix property (polymer_chemprop_b200.BatchMolGraph verifies it exactly per molecule). */
+int wd_expand_features(const float* f_atoms, const float* bond_tail, const int64_t* b2a, int64_t n_atoms,
+                       int64_t n_bonds, int32_t atom_fdim, int32_t tail_fdim, float* f_atoms_out,
+                       int32_t ld_atoms, float* f_bonds_out, int32_t ld_bonds, void* stream);
+
 /* Bytes of caller-provided workspace.  The forward pass stores there what the backward pass
  * re-reads (I, M_t, A_t, H) plus scratch; pass the same buffer, untouched, to the backward. */
 size_t wd_workspace_bytes(const WdConfig* cfg, int64_t n_atoms, int64_t n_bonds, int64_t n_mols);
 
-/* out[G, h] = MPNEncoder.forward(graph)  (mpn.py:92-171, bond messages, dropout 0). */
+/* out[G, h] = MPNEncoder.forward(graph)  (mpn.py:92-171, bond messages; dropout per cfg->dropout). */
 int wd_encoder_forward(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,
                        void* workspace, size_t workspace_bytes, float* out, void* stream);
+
+/* Forward only (chemprop/train/predict.py:10-68, molecule_fingerprint.py:151-183 run the encoder under
+ * torch.no_grad()): same kernels and results as wd_encoder_forward, but nothing is kept for a backward pass --
+ * two alternating message buffers, one aggregate buffer, no S_t copy, no gradient scratch (~3.3 instead of ~10
+ * [N_b, h] buffers at depth 3).  cfg->dropout is honoured as given (0 for model.eval()). */
+size_t wd_infer_workspace_bytes(const WdConfig* cfg, int64_t n_atoms, int64_t n_bonds, int64_t n_mols);
+int wd_encoder_infer(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg, void* workspace,
+                     size_t workspace_bytes, float* out, void* stream);
 
 /* Gradients of sum(out * d_out) w.r.t. the weights; deterministic (no atomics). */
 int wd_encoder_backward(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,

@@ -36,10 +36,41 @@ def _act(name: str):
     return table[name]
 
 
+def philox4x32_10(c0, c1, c2, c3, k0, k1):
+    """Philox4x32-10 (Salmon et al., SC'11) on numpy uint64 arrays holding 32-bit words; the product's
+    dropout masks are words of this generator (csrc/common.cuh philox4x32_10)."""
+    m32 = np.uint64(0xFFFFFFFF)
+    c0, c1, c2, c3 = (np.asarray(x, dtype=np.uint64) & m32 for x in (c0, c1, c2, c3))
+    k0, k1 = np.uint64(k0), np.uint64(k1)
+    for _ in range(10):
+        p0 = np.uint64(0xD2511F53) * c0
+        p1 = np.uint64(0xCD9E8D57) * c2
+        c0, c1, c2, c3 = ((p1 >> np.uint64(32)) ^ c1 ^ k0) & m32, p1 & m32, ((p0 >> np.uint64(32)) ^ c3 ^ k1) & m32, p0 & m32
+        k0 = (k0 + np.uint64(0x9E3779B9)) & m32
+        k1 = (k1 + np.uint64(0xBB67AE85)) & m32
+    return c0, c1, c2, c3
+
+
+def dropout_multiplier(n_rows: int, n_cols: int, ld: int, p: float, seed_lo: int, seed_hi: int, salt: int) -> torch.Tensor:
+    """The product's dropout mask of one [n_rows, ld]-strided activation as a float32 [n_rows, n_cols] tensor of
+    0 or 1/(1-p): element e = row * ld + col is dropped iff word (e & 3) of Philox(counter = (e >> 2, salt, 0),
+    key = seed) is below floor(p * 2^32)   (csrc/common.cuh dropout_keep4; nn.Dropout at mpn.py:124 / :134)."""
+    e = (np.arange(n_rows, dtype=np.uint64)[:, None] * np.uint64(ld) + np.arange(n_cols, dtype=np.uint64)[None, :])
+    q = e >> np.uint64(2)
+    words = philox4x32_10(q & np.uint64(0xFFFFFFFF), q >> np.uint64(32), np.uint64(salt), np.uint64(0), seed_lo, seed_hi)
+    lane = (e & np.uint64(3)).astype(np.int64)
+    w = np.choose(lane, words)
+    thresh = np.uint64(min(4294967295, int(np.floor(float(np.float32(p)) * 4294967296.0))))
+    scale = np.float32(1.0) / (np.float32(1.0) - np.float32(p))
+    return torch.from_numpy(np.where(w < thresh, np.float32(0.0), scale).astype(np.float32))
+
+
 def encoder_forward(components, weights: Dict[str, torch.Tensor], depth: int,
                     activation: str = "ReLU", undirected: bool = False,
-                    aggregation: str = "mean", aggregation_norm: float = 100.0) -> torch.Tensor:
-    """MPNEncoder.forward, bond-message branch (mpn.py:81-173), dropout 0.
+                    aggregation: str = "mean", aggregation_norm: float = 100.0, dropout=None) -> torch.Tensor:
+    """MPNEncoder.forward, bond-message branch (mpn.py:81-173).  ``dropout`` = None (p = 0 / eval) or a dict
+    {p, seed_lo, seed_hi, ld} selecting the product's Philox masks (the reference's own RNG stream cannot be
+    shared with a CUDA kernel; the op sequence -- mask * 1/(1-p) after each activation, :124 and :134 -- is the same).
 
     ``weights`` uses the reference's parameter names: W_i.weight, W_h.weight, W_o.weight,
     W_o.bias and optionally W_i.bias / W_h.bias (mpn.py:47-57).
@@ -49,7 +80,7 @@ def encoder_forward(components, weights: Dict[str, torch.Tensor], depth: int,
     lin = torch.nn.functional.linear
     inp = lin(f_bonds, weights["W_i.weight"], weights.get("W_i.bias"))           # mpn.py:96
     message = act(inp)                                                             # :97
-    for _ in range(depth - 1):                                                     # :100
+    for _ in range(depth - 1):                                                     # :100  (step t = _ + 1)
         if undirected:
             message = (message + message[b2revb]) / 2                              # :101-102
         nei_msg = index_select_nd(message, a2b)                                    # :112
@@ -58,11 +89,18 @@ def encoder_forward(components, weights: Dict[str, torch.Tensor], depth: int,
         message = a_message[b2a] - message[b2revb]                                 # :119-120 (reverse unweighted)
         message = lin(message, weights["W_h.weight"], weights.get("W_h.bias"))    # :122
         message = act(inp + message)                                               # :123
+        if dropout:                                                                # :124
+            message = message * dropout_multiplier(message.shape[0], message.shape[1], dropout["ld"], dropout["p"],
+                                                   dropout["seed_lo"], dropout["seed_hi"], _ + 1).to(message.dtype)
     nei_msg = index_select_nd(message, a2b)                                        # :127
     nei_w = index_select_nd(w_bonds, a2b)                                          # :128
     a_message = (nei_msg * nei_w[..., None]).sum(dim=1)                            # :130-131
     a_input = torch.cat([f_atoms, a_message], dim=1)                               # :132
     atom_hiddens = act(lin(a_input, weights["W_o.weight"], weights["W_o.bias"]))  # :133
+    if dropout:                                                                    # :134
+        atom_hiddens = atom_hiddens * dropout_multiplier(atom_hiddens.shape[0], atom_hiddens.shape[1], dropout["ld"],
+                                                         dropout["p"], dropout["seed_lo"], dropout["seed_hi"],
+                                                         depth).to(atom_hiddens.dtype)
     mol_vecs = []
     zero = torch.zeros(atom_hiddens.shape[1], dtype=atom_hiddens.dtype)
     for i, (a_start, a_size) in enumerate(a_scope):                                # :147-169

@@ -23,7 +23,8 @@ class WdConfig(C.Structure):
     _fields_ = [("hidden_size", C.c_int32), ("atom_fdim", C.c_int32), ("bond_fdim", C.c_int32),
                 ("depth", C.c_int32), ("activation", C.c_int32), ("aggregation", C.c_int32),
                 ("undirected", C.c_int32), ("bias", C.c_int32), ("math_mode", C.c_int32),
-                ("aggregation_norm", C.c_float)]
+                ("aggregation_norm", C.c_float), ("dropout", C.c_float), ("dropout_seed_lo", C.c_uint32),
+                ("dropout_seed_hi", C.c_uint32)]
 
 
 class WdGraph(C.Structure):
@@ -43,14 +44,15 @@ class WdGrads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("dW_i", "db_i", "dW_h", "db_h", "dW_o", "db_o")]
 
 
-EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_workspace_bytes", "wd_encoder_forward",
+EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_workspace_bytes", "wd_encoder_forward",
+           "wd_infer_workspace_bytes", "wd_encoder_infer",
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
            "wd_debug_dw", "wd_debug_timing")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
-ABI_VERSION = 2      # include/wdmpnn.h: WdGraph gained ld_atoms / ld_bonds
+ABI_VERSION = 3      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features
 _lib = None
 
 
@@ -69,6 +71,9 @@ def lib():
     vp = C.c_void_p
     L.wd_csr_build.argtypes = [vp, C.c_int64, C.c_int64, vp, vp, C.c_int64, vp, vp, C.c_int64] + [vp] * 8 + [vp]
     L.wd_csr_build.restype = C.c_int
+    L.wd_expand_features.argtypes = [vp, vp, vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, vp, C.c_int32, vp,
+                                     C.c_int32, vp]
+    L.wd_expand_features.restype = C.c_int
     L.wd_csr_build_check.argtypes = [vp, vp]
     L.wd_csr_build_check.restype = C.c_int
     L.wd_workspace_bytes.argtypes = [C.POINTER(WdConfig), C.c_int64, C.c_int64, C.c_int64]
@@ -76,6 +81,10 @@ def lib():
     L.wd_encoder_forward.argtypes = [C.POINTER(WdGraph), C.POINTER(WdWeights), C.POINTER(WdConfig), vp,
                                      C.c_size_t, vp, vp]
     L.wd_encoder_forward.restype = C.c_int
+    L.wd_infer_workspace_bytes.argtypes = L.wd_workspace_bytes.argtypes
+    L.wd_infer_workspace_bytes.restype = C.c_size_t
+    L.wd_encoder_infer.argtypes = L.wd_encoder_forward.argtypes
+    L.wd_encoder_infer.restype = C.c_int
     L.wd_encoder_backward.argtypes = [C.POINTER(WdGraph), C.POINTER(WdWeights), C.POINTER(WdConfig), vp,
                                       C.c_size_t, vp, C.POINTER(WdGrads), vp]
     L.wd_encoder_backward.restype = C.c_int

@@ -7,6 +7,8 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <utility>
 
 #include "../../include/wdmpnn.h"
 
@@ -42,14 +44,47 @@ struct ProfScope {  // sets the category of the launches issued while it is aliv
   ~ProfScope() { g_prof_cat = prev; }
 };
 
+// Programmatic dependent launch (PDL).  Every kernel of this library starts with pdl_prologue() and is launched
+// with programmaticStreamSerializationAllowed: the next kernel in the stream is scheduled while its predecessor
+// drains (the implicit trigger when the predecessor's CTAs exit) and blocks in `griddepcontrol.wait` until the
+// predecessor has completed and flushed its memory -- so no kernel touches memory before its predecessor is done;
+// only launch latency and CTA ramp-up overlap with the predecessor's tail.  Measured on B200 (profiles/
+// r1_j_pdl_variants.txt): 2.72 -> 2.68 ms/step at batch 4096, 0.540 -> 0.473 at 512, 0.290 -> 0.268 at 50.
+// An EARLY trigger (`griddepcontrol.launch_dependents` at the top of every kernel) was measured too and is
+// slower at large batches (2.90 ms): the dependents' CTAs become resident long before they can run.
+// The wait is a no-op for launches without the attribute (WD_PDL=0, or profiling with events between launches).
+__device__ __forceinline__ void pdl_prologue() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+extern int g_pdl;   // -1 = read WD_PDL from the environment on first use (default on)
+inline bool pdl_enabled() {
+  if (g_pdl < 0) { const char* e = getenv("WD_PDL"); g_pdl = (e && atoi(e) == 0) ? 0 : 1; }
+  return g_pdl != 0;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = (pdl_enabled() && !g_prof_on) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 // Every kernel launch goes through this so wd_launch_count() is exact.
 #define WD_LAUNCH(kernel, grid, block, smem, stream, ...)                                   \
   do {                                                                                      \
     if (wd::g_prof_on) wd::prof_begin(stream);                                              \
-    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                             \
+    cudaError_t _e = wd::launch_kernel(kernel, (grid), (block), (smem), (stream), __VA_ARGS__); \
     if (wd::g_prof_on) wd::prof_end(stream);                                                \
     wd::g_launches.fetch_add(1, std::memory_order_relaxed);                                 \
-    cudaError_t _e = cudaGetLastError();                                                    \
+    if (_e == cudaSuccess) _e = cudaGetLastError();                                         \
     if (_e != cudaSuccess)                                                                  \
       return wd::fail(WD_ERR_CUDA, "launch of %s failed: %s (%s:%d)", #kernel,              \
                       cudaGetErrorString(_e), __FILE__, __LINE__);                          \
@@ -81,6 +116,51 @@ __device__ __forceinline__ float act_bwd_from_out(float y) {
   if (ACT == WD_ACT_TANH) return 1.f - y * y;
   if (ACT == WD_ACT_SELU) return y > 0.f ? kSeluScale : y + kSeluScale * kSeluAlpha;
   return y > 0.f ? 1.f : y + 1.f;
+}
+
+// ---- dropout (nn.Dropout, mpn.py:38; applied at :124 and :134) --------------------------------
+// The keep/drop decision of element e (= row * ld + col of the [rows, ld] activation) is word (e & 3) of
+// Philox4x32-10 with counter (e >> 2, salt, 0) and key = seed: stateless, so the backward regenerates the
+// mask instead of storing it, and the CPU oracle can reproduce it exactly (oracle/mpn_oracle.py).
+struct Dropout {
+  uint32_t thresh;            // drop iff word < thresh (= p * 2^32); 0 = dropout off (p == 0 / eval mode)
+  float scale;                // 1 / (1 - p)
+  uint32_t seed_lo, seed_hi;  // key
+  uint32_t salt;              // site: depth step t = 1 .. d-1, d = atom hiddens
+};
+
+__host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                       uint32_t k0, uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// multipliers (0 or scale) of the four elements e .. e+3 (e % 4 == 0)
+__device__ __forceinline__ float4 dropout_keep4(const Dropout& d, int64_t e) {
+  uint32_t w[4];
+  const uint64_t q = (uint64_t)e >> 2;
+  philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), d.salt, 0u, d.seed_lo, d.seed_hi, w);
+  return make_float4(w[0] < d.thresh ? 0.f : d.scale, w[1] < d.thresh ? 0.f : d.scale,
+                     w[2] < d.thresh ? 0.f : d.scale, w[3] < d.thresh ? 0.f : d.scale);
+}
+__device__ __forceinline__ float4 dropout4(float4 x, const Dropout& d, int64_t e) {
+  const float4 k = dropout_keep4(d, e);
+  return make_float4(x.x * k.x, x.y * k.y, x.z * k.z, x.w * k.w);
+}
+// d act(z)/dz * keep * scale from the STORED (post-dropout) activation y = keep * scale * act(z)
+template <int ACT>
+__device__ __forceinline__ float4 act_bwd_dropped4(float4 y, const Dropout& d, int64_t e) {
+  const float4 k = dropout_keep4(d, e);
+  const float inv = 1.f / d.scale;
+  return make_float4(act_bwd_from_out<ACT>(y.x * inv) * k.x, act_bwd_from_out<ACT>(y.y * inv) * k.y,
+                     act_bwd_from_out<ACT>(y.z * inv) * k.z, act_bwd_from_out<ACT>(y.w * inv) * k.w);
 }
 
 #define WD_DISPATCH_ACT(act, ...)                                          \

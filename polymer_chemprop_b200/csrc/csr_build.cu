@@ -43,6 +43,7 @@ __device__ __forceinline__ int block_excl_scan(int v, int* total) {
 __global__ void k_csr_degree(const int64_t* __restrict__ a2b, int64_t n_atoms, int K,
                              int32_t* __restrict__ in_ptr, int32_t* __restrict__ block_sums,
                              int32_t* __restrict__ flags) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t a = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
   int deg = 0;
   if (a < n_atoms) {
@@ -61,6 +62,7 @@ __global__ void k_csr_degree(const int64_t* __restrict__ a2b, int64_t n_atoms, i
 
 // phase 2: one block scans the per-block totals in place (exclusive), carrying across chunks.
 __global__ void k_csr_scan_blocks(int32_t* __restrict__ block_sums, int n_blocks) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   __shared__ int carry;
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
@@ -84,6 +86,7 @@ __global__ void k_csr_fill(const int64_t* __restrict__ a2b, const int64_t* __res
                            const int32_t* __restrict__ block_sums, int32_t* __restrict__ in_ptr,
                            int32_t* __restrict__ in_idx, int32_t* __restrict__ out_idx,
                            int32_t* __restrict__ dst, int32_t* __restrict__ flags) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t a = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
   if (a >= n_atoms) return;
   int base = in_ptr[a] + block_sums[blockIdx.x];
@@ -116,6 +119,7 @@ __global__ void k_csr_bonds(const int64_t* __restrict__ b2a, const int64_t* __re
                             int64_t n_atoms, int64_t n_bonds, const int32_t* __restrict__ in_ptr,
                             int32_t* __restrict__ src, int32_t* __restrict__ rev,
                             int32_t* __restrict__ dst, int32_t* __restrict__ flags) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= n_bonds) return;
   int64_t s = b2a[b], r = b2revb[b];
@@ -138,6 +142,7 @@ __global__ void k_csr_bonds(const int64_t* __restrict__ b2a, const int64_t* __re
 __global__ void k_csr_mols(const int32_t* __restrict__ a_start, const int32_t* __restrict__ a_size,
                            int64_t n_mols, int64_t n_atoms, int32_t* __restrict__ mol_of,
                            int32_t* __restrict__ flags) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   // one warp per molecule, lanes stride over its atoms
   int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;

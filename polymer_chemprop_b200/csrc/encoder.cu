@@ -1,6 +1,9 @@
 // C-ABI entry points and kernel sequencing of the wD-MPNN encoder (include/wdmpnn.h).
 // Forward  == chemprop/models/mpn.py:92-171 (bond messages, dropout 0).
 // Backward == autograd of the same, restated as deterministic CSR kernels.
+#include <algorithm>
+#include <cmath>
+
 #include "common.cuh"
 #include "graph_kernels.cuh"
 #include "operands.cuh"
@@ -36,7 +39,9 @@ int dw_chunks(int64_t rows, int n1, int n2) {
   return (int)std::max<int64_t>(1, std::min<int64_t>(z, 64));
 }
 
-Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
+// infer: forward-only layout (wd_encoder_infer) -- two alternating message buffers, one aggregate buffer, nothing
+// kept for a backward pass (no S_t, no gradient scratch).
+Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool infer = false) {
   Layout L;
   const int h = c.hidden_size;
   L.ldh = (int)round_up(h, 8);   // rows start on 32-byte sectors: a 128-byte row chunk is exactly 4 sectors
@@ -45,18 +50,18 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   int64_t off = 0;
   auto take = [&](int64_t n) { int64_t o = off; off += round_up(n, 64); return o; };
   L.I = take(L.szB);
-  L.M = take((int64_t)std::max(0, c.depth - 1) * L.szB);
-  L.Agg = take((int64_t)c.depth * L.szA);
+  L.M = take((int64_t)(infer ? std::min(2, std::max(0, c.depth - 1)) : std::max(0, c.depth - 1)) * L.szB);
+  L.Agg = take((int64_t)(infer ? 1 : c.depth) * L.szA);
   L.H = take(L.szA);
   L.mscale = take(G);
   L.U = take(c.undirected ? L.szB : 0);
-  L.S = take(c.math_mode == WD_MATH_TF32 ? (int64_t)std::max(0, c.depth - 1) * L.szB : 0);
-  L.dZ = take(L.szB);
-  L.dZ2 = take(c.depth > 2 ? L.szB : 0);
-  L.dS = take(L.szB);
-  L.dI = take(L.szB);
-  L.dA = take(L.szA);
-  L.dZo = take(L.szA);
+  L.S = take(c.math_mode == WD_MATH_TF32 && !infer ? (int64_t)std::max(0, c.depth - 1) * L.szB : 0);
+  L.dZ = take(infer ? 0 : L.szB);
+  L.dZ2 = take(c.depth > 2 && !infer ? L.szB : 0);
+  L.dS = take(infer ? 0 : L.szB);
+  L.dI = take(infer ? 0 : L.szB);
+  L.dA = take(infer ? 0 : L.szA);
+  L.dZo = take(infer ? 0 : L.szA);
   const int Fo = c.atom_fdim + h;
   if (c.math_mode == WD_MATH_TF32) {
     L.Zh = tc_dw_z(Nb, h, tc_dw_count_tiles(h, 0));
@@ -70,14 +75,14 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G) {
   L.Z = std::max(std::max(L.Zh, L.Zi), L.Zo);
   int64_t pw = std::max<int64_t>((int64_t)std::max(1, c.depth - 1) * h * h,
                                  (int64_t)h * std::max(Fo, c.bond_fdim));
-  L.partials = take((int64_t)L.Z * pw + (int64_t)kColsumMaxChunks * h);
+  L.partials = take(infer ? 0 : (int64_t)L.Z * pw + (int64_t)kColsumMaxChunks * h);
   L.pWi = tc_packed_geometry(h, c.bond_fdim, 0);     // I = f_bonds W_i^T
   L.pWh = tc_packed_geometry(h, h, 0, tc_use_gemm4() ? T4_MAX_BN : T2_MAX_BN);   // S W_h^T (gathered depth step)
   L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
   L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h
   L.pWoT = tc_packed_geometry(h, h, 0);              // dA_d = dZo W_o[:, F_a:]
   const TcPacked* pk[5] = {&L.pWi, &L.pWh, &L.pWo, &L.pWhT, &L.pWoT};
-  for (int i = 0; i < 5; ++i) L.pk[i] = take(c.math_mode == WD_MATH_TF32 ? pk[i]->floats() : 0);
+  for (int i = 0; i < 5; ++i) L.pk[i] = take(c.math_mode == WD_MATH_TF32 && !(infer && i >= 3) ? pk[i]->floats() : 0);
   L.total = off;
   return L;
 }
@@ -92,6 +97,8 @@ int check_cfg(const WdConfig* c) {
     return fail(WD_ERR_INVALID_ARG, "aggregation %d unknown", c->aggregation);
   if (c->math_mode != WD_MATH_FP32 && c->math_mode != WD_MATH_TF32)
     return fail(WD_ERR_INVALID_ARG, "math_mode %d unknown", c->math_mode);
+  if (!(c->dropout >= 0.f && c->dropout < 1.f))
+    return fail(WD_ERR_INVALID_ARG, "dropout %g must be in [0, 1)", (double)c->dropout);
   return WD_OK;
 }
 
@@ -111,16 +118,30 @@ int check_graph(const WdGraph* g, const WdWeights* w, const WdConfig* c) {
   return WD_OK;
 }
 
+// dropout site `salt` (depth step t = 1 .. d-1, d = atom hiddens) of this call; thresh == 0 switches it off
+Dropout make_dropout(const WdConfig& c, int salt) {
+  Dropout d{};
+  if (c.dropout > 0.f) {
+    d.thresh = (uint32_t)std::min<double>(4294967295.0, std::floor((double)c.dropout * 4294967296.0));
+    d.scale = 1.f / (1.f - c.dropout);
+    d.seed_lo = c.dropout_seed_lo;
+    d.seed_hi = c.dropout_seed_hi;
+    d.salt = (uint32_t)salt;
+  }
+  return d;
+}
+
 inline int grid1d(int64_t n, int block = 256) { return (int)ceil_div(std::max<int64_t>(n, 1), block); }
 
 // ---- contraction dispatch: FP32 -> SIMT FFMA kernels, TF32 -> tcgen05 kernels (tc == packed weights) ----
 template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
 int gemm(const WdConfig& c, cudaStream_t s, const AOperand& A, const float* W, int ldb, const float* bias,
-         const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, const TcPacked* tc) {
-  if (c.math_mode == WD_MATH_TF32) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M);
+         const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, const TcPacked* tc,
+         const Dropout& drop = Dropout{}) {
+  if (c.math_mode == WD_MATH_TF32) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M, drop);
   dim3 grid((unsigned)ceil_div(M, SG_BM), (unsigned)ceil_div(std::max(N, ldc), SG_BN));
   WD_LAUNCH((k_simt_gemm<AMODE, BMODE, EPI, ACT, PREACT>), grid, SG_THREADS, 0, s, A, W, ldb, bias, R, ldr,
-            C, ldc, M, N, K);
+            C, ldc, M, N, K, drop);
   return WD_OK;
 }
 
@@ -163,8 +184,8 @@ int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_
 // ---- forward ----------------------------------------------------------------------------------
 template <int ACT>
 int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, float* out,
-                 cudaStream_t s) {
-  Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
+                 cudaStream_t s, bool infer) {
+  Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols, infer);
   const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim;
   const int64_t Na = g.n_atoms, Nb = g.n_bonds, G = g.n_mols;
   float* I = L.p(ws, L.I);
@@ -183,8 +204,8 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   const float* prev = I;   // message = act(input) is applied on load (PREACT)          :97
   for (int t = 1; t < c.depth; ++t) {                                               // :100
     const bool pre = (t == 1);
-    float* A_t = L.p(ws, L.Agg) + (int64_t)(t - 1) * L.szA;
-    float* M_t = L.p(ws, L.M) + (int64_t)(t - 1) * L.szB;
+    float* A_t = L.p(ws, L.Agg) + (int64_t)(infer ? 0 : t - 1) * L.szA;
+    float* M_t = L.p(ws, L.M) + (int64_t)(infer ? (t - 1) & 1 : t - 1) * L.szB;
     const float* u = prev;
     bool upre = pre;
     if (c.undirected) {                                                             // :101-102
@@ -201,21 +222,23 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     ProfScope ps(WD_PROF_DEPTH_STEP);
     // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
     AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
-    if (c.math_mode == WD_MATH_TF32 && !tc_use_v1()) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
+    if (c.math_mode == WD_MATH_TF32 && !tc_use_v1() && !infer) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
     const float* bh = c.bias ? w.b_h : nullptr;
-    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh)));
-    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh)));
+    const Dropout drop = make_dropout(c, t);                                          // :124
+    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh, drop)));
+    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh, drop)));
     prev = M_t;
   }
   // final aggregate + atom update                                                    :127-134
-  float* A_d = L.p(ws, L.Agg) + (int64_t)(c.depth - 1) * L.szA;
+  float* A_d = L.p(ws, L.Agg) + (int64_t)(infer ? 0 : c.depth - 1) * L.szA;
   { ProfScope ps(WD_PROF_AGGREGATE);
   if (c.depth == 1) WD_LAUNCH((k_aggregate<ACT, true>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4);
   else              WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4); }
   float* H = L.p(ws, L.H);
   AOperand a_o{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
   { ProfScope ps(WD_PROF_ATOM_UPDATE);
-  WD_TRY((gemm<A_CONCAT, B_NK, E_ACT, ACT, false>(c, s, a_o, w.W_o, Fa + h, w.b_o, nullptr, 0, H, ld, Na, h, Fa + h, &L.pWo))); }
+  WD_TRY((gemm<A_CONCAT, B_NK, E_ACT, ACT, false>(c, s, a_o, w.W_o, Fa + h, w.b_o, nullptr, 0, H, ld, Na, h, Fa + h, &L.pWo,
+                                                  make_dropout(c, c.depth)))); }                 // :133-134
   // readout                                                                          :146-171
   if (G > 0) {
     ProfScope ps(WD_PROF_READOUT);
@@ -230,16 +253,16 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
 // ---- backward ---------------------------------------------------------------------------------
 template <int ACT, bool PREACT, bool HAS_DS, bool WRITE_DZ, bool WRITE_DI>
 int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const float* dA, const float* dS,
-                 const float* Y, int ld, float* dZ, const float* dI_in, float* dI) {
+                 const float* Y, int ld, float* dZ, const float* dI_in, float* dI, const Dropout& drop) {
   const int nc4 = ld / 4;
   const int64_t Nb = g.n_bonds;
   ProfScope ps(WD_PROF_MSG_GRAD);
   if (c.undirected && HAS_DS)
     WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
-              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4);
+              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop);
   else
     WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
-              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4);
+              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop);
   return WD_OK;
 }
 
@@ -266,10 +289,10 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   { ProfScope ps(WD_PROF_READOUT);
   if (h % 4 == 0 && (reinterpret_cast<uintptr_t>(d_out) & 15) == 0)
     WD_LAUNCH((k_readout_grad<ACT, true>), grid1d(Na * nc4), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
-              L.p(ws, L.mscale), dZo, Na);
+              L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth));
   else
     WD_LAUNCH((k_readout_grad<ACT, false>), grid1d(Na * nc4), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
-              L.p(ws, L.mscale), dZo, Na); }
+              L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth)); }
   {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zo;
@@ -295,8 +318,8 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     const float* M_prev = (t == 1) ? I : L.p(ws, L.M) + (int64_t)(t - 2) * L.szB;
     const bool pre = (t == 1);
     // dZ_t = dM_t * act'(M_t), dI += dZ_t ; dM_t = w_b dA[dst b] - dS[rev b] (symmetrised if undirected)
-    if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI))); sum = dZ; }
-    else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI))); sum = dI; }
+    if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI, make_dropout(c, t)))); sum = dZ; }
+    else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI, make_dropout(c, t)))); sum = dI; }
     // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
     const float* u = M_prev;
     bool upre = pre;
@@ -327,11 +350,11 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     { ProfScope ps(WD_PROF_DW);
     WD_TRY(reduce_partials(s, P, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
     if (c.bias && gr.db_h) WD_TRY(colsum(s, sum, ld, Pcol, gr.db_h, Nb, h, Zh)); }  // sum == sum_{t>=1} dZ_t here
-    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI)));
+    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI, Dropout{})));
   } else {
     WD_CUDA_OK(cudaMemsetAsync(gr.dW_h, 0, sizeof(float) * h * h, s));
     if (c.bias && gr.db_h) WD_CUDA_OK(cudaMemsetAsync(gr.db_h, 0, sizeof(float) * h, s));
-    WD_TRY((message_grad<ACT, true, false, false, true>(c, s, g, dA, dS, I, ld, nullptr, nullptr, dI)));
+    WD_TRY((message_grad<ACT, true, false, false, true>(c, s, g, dA, dS, I, ld, nullptr, nullptr, dI, Dropout{})));
   }
   {  // dW_i = dI^T f_bonds ; db_i = colsum(dI)
     ProfScope ps(WD_PROF_DW);
@@ -365,7 +388,28 @@ extern "C" int wd_encoder_forward(const WdGraph* graph, const WdWeights* weights
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
   int rc = WD_OK;
-  WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream));
+  WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream, false));
+  return rc;
+}
+
+extern "C" size_t wd_infer_workspace_bytes(const WdConfig* cfg, int64_t n_atoms, int64_t n_bonds, int64_t n_mols) {
+  if (wd::check_cfg(cfg) != WD_OK || n_atoms < 1 || n_bonds < 1 || n_mols < 0) return 0;
+  return (size_t)wd::make_layout(*cfg, n_atoms, n_bonds, n_mols, true).total * sizeof(float);
+}
+
+extern "C" int wd_encoder_infer(const WdGraph* graph, const WdWeights* weights, const WdConfig* cfg,
+                                void* workspace, size_t workspace_bytes, float* out, void* stream) {
+  using namespace wd;
+  WD_TRY(check_cfg(cfg));
+  WD_TRY(check_graph(graph, weights, cfg));
+  if (!workspace || (graph->n_mols > 0 && !out)) return fail(WD_ERR_INVALID_ARG, "workspace/out is NULL");
+  if (workspace_bytes < wd_infer_workspace_bytes(cfg, graph->n_atoms, graph->n_bonds, graph->n_mols))
+    return fail(WD_ERR_INVALID_ARG, "workspace too small: %zu < %zu bytes", workspace_bytes,
+                wd_infer_workspace_bytes(cfg, graph->n_atoms, graph->n_bonds, graph->n_mols));
+  if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
+    return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
+  int rc = WD_OK;
+  WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream, true));
   return rc;
 }
 
@@ -388,7 +432,6 @@ extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weight
 
 extern "C" const char* wd_last_error(void) { return wd::g_err; }
 extern "C" int64_t wd_launch_count(void) { return wd::g_launches.load(); }
-extern "C" int wd_abi_version(void) { return 2; }
 
 // ---- test hooks: the raw contractions behind the encoder, on plain operands ----------------------
 // C[M, ldc] = epi(A[M, K] * B^T (+ bias) (+ R)), B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k].

@@ -14,6 +14,7 @@ template <int ACT, bool PREACT>
 __global__ void k_aggregate(const float* __restrict__ U, int ld, const float* __restrict__ w,
                             const int32_t* __restrict__ ptr, const int32_t* __restrict__ idx,
                             float* __restrict__ out, int64_t n_rows, int nc4) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_rows * nc4) return;
   int64_t a = i / nc4;
@@ -46,6 +47,7 @@ __global__ void k_aggregate(const float* __restrict__ U, int ld, const float* __
 template <int ACT, bool PREACT>
 __global__ void k_symmetrize(const float* __restrict__ X, int ld, const int32_t* __restrict__ rev,
                              float* __restrict__ U, int64_t n_rows, int nc4) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_rows * nc4) return;
   int64_t b = i / nc4;
@@ -65,7 +67,9 @@ template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool WRITE_DZ, boo
 __global__ void k_message_grad(const float* __restrict__ dA, const float* __restrict__ dS,
                                const float* __restrict__ Y, int ld, const float* __restrict__ w,
                                const int32_t* __restrict__ dst, const int32_t* __restrict__ rev,
-                               float* __restrict__ dZ, const float* dI_in, float* dI, int64_t n_rows, int nc4) {
+                               float* __restrict__ dZ, const float* dI_in, float* dI, int64_t n_rows, int nc4,
+                               Dropout drop) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_rows * nc4) return;
   int64_t b = i / nc4;
@@ -87,8 +91,11 @@ __global__ void k_message_grad(const float* __restrict__ dA, const float* __rest
   }
   float4 y = ldg4(Y + b * ld + c);
   if (PREACT) y = f4_act<ACT>(y);
-  float4 dz = make_float4(g.x * act_bwd_from_out<ACT>(y.x), g.y * act_bwd_from_out<ACT>(y.y),
-                          g.z * act_bwd_from_out<ACT>(y.z), g.w * act_bwd_from_out<ACT>(y.w));
+  float4 dy;                                   // d (stored activation) / d (pre-activation)
+  if (!PREACT && drop.thresh != 0u) dy = act_bwd_dropped4<ACT>(y, drop, b * ld + c);   // Y = dropout(act(z)), mpn.py:124
+  else dy = make_float4(act_bwd_from_out<ACT>(y.x), act_bwd_from_out<ACT>(y.y), act_bwd_from_out<ACT>(y.z),
+                        act_bwd_from_out<ACT>(y.w));
+  float4 dz = make_float4(g.x * dy.x, g.y * dy.y, g.z * dy.z, g.w * dy.w);
   if (WRITE_DZ) st4(dZ + b * ld + c, dz);
   if (WRITE_DI) {
     if (dI_in != nullptr) {
@@ -105,6 +112,7 @@ __global__ void k_mol_scale(const float* __restrict__ w_atoms, const int32_t* __
                             const int32_t* __restrict__ a_size, const float* __restrict__ dop,
                             int aggregation, float aggregation_norm, float* __restrict__ mscale,
                             int64_t n_mols) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= n_mols) return;
   int s = a_start[g], n = a_size[g];
@@ -124,6 +132,7 @@ __global__ void k_readout(const float* __restrict__ H, int ld, const float* __re
                           const int32_t* __restrict__ a_start, const int32_t* __restrict__ a_size,
                           const float* __restrict__ mscale, float* __restrict__ out, int h,
                           int64_t n_mols) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_mols * h) return;
   int64_t g = i / h;
@@ -139,7 +148,8 @@ template <int ACT, bool VEC4>
 __global__ void k_readout_grad(const float* __restrict__ d_out, int h, const float* __restrict__ H,
                                int ld, const float* __restrict__ w_atoms,
                                const int32_t* __restrict__ mol_of, const float* __restrict__ mscale,
-                               float* __restrict__ dZo, int64_t n_atoms) {
+                               float* __restrict__ dZo, int64_t n_atoms, Dropout drop) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   const int nc4 = ld / 4;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_atoms * nc4) return;
@@ -160,10 +170,14 @@ __global__ void k_readout_grad(const float* __restrict__ d_out, int h, const flo
       d.z = c + 2 < h ? __ldg(dp + 2) : 0.f;
       d.w = c + 3 < h ? __ldg(dp + 3) : 0.f;
     }
-    v.x = s * d.x * act_bwd_from_out<ACT>(y.x);
-    v.y = c + 1 < h ? s * d.y * act_bwd_from_out<ACT>(y.y) : 0.f;
-    v.z = c + 2 < h ? s * d.z * act_bwd_from_out<ACT>(y.z) : 0.f;
-    v.w = c + 3 < h ? s * d.w * act_bwd_from_out<ACT>(y.w) : 0.f;
+    float4 dy;                                 // H = dropout(act(z)), mpn.py:133-134
+    if (drop.thresh != 0u) dy = act_bwd_dropped4<ACT>(y, drop, a * ld + c);
+    else dy = make_float4(act_bwd_from_out<ACT>(y.x), act_bwd_from_out<ACT>(y.y), act_bwd_from_out<ACT>(y.z),
+                          act_bwd_from_out<ACT>(y.w));
+    v.x = s * d.x * dy.x;
+    v.y = c + 1 < h ? s * d.y * dy.y : 0.f;
+    v.z = c + 2 < h ? s * d.z * dy.z : 0.f;
+    v.w = c + 3 < h ? s * d.w * dy.w : 0.f;
   }
   st4(dZo + a * ld + c, v);
 }

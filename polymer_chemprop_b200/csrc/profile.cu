@@ -7,6 +7,7 @@
 namespace wd {
 
 bool g_prof_on = false;
+int g_pdl = -1;
 thread_local int g_prof_cat = WD_PROF_MISC;
 
 namespace {
@@ -67,3 +68,6 @@ extern "C" int wd_profile_read(int category, double* total_ms, int64_t* launches
   *launches = n;
   return WD_OK;
 }
+
+// ABI version of include/wdmpnn.h (3: wd_expand_features, wd_encoder_infer, WdConfig.dropout*)
+extern "C" int wd_abi_version(void) { return 3; }

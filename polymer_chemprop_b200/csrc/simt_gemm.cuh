@@ -15,7 +15,8 @@ template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
 __global__ void __launch_bounds__(SG_THREADS)
 k_simt_gemm(AOperand A, const float* __restrict__ W, int ldb, const float* __restrict__ bias,
             const float* __restrict__ R, int ldr, float* __restrict__ C, int ldc, int64_t M, int N,
-            int K) {
+            int K, Dropout drop) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   __shared__ float As[SG_BK][SG_BM + 4];
   __shared__ float Bs[SG_BK][SG_BN + 4];
   const int tid = threadIdx.x;
@@ -99,7 +100,9 @@ k_simt_gemm(AOperand A, const float* __restrict__ W, int ldb, const float* __res
       if (EPI != E_STORE) v = act_fwd<ACT>(v);
       o[j] = (n0 + j < N) ? v : 0.f;   // pad columns [N, ldc) are kept at zero
     }
-    st4(C + r * ldc + n0, make_float4(o[0], o[1], o[2], o[3]));  // ldc % 4 == 0, n0 % 4 == 0
+    float4 o4 = make_float4(o[0], o[1], o[2], o[3]);
+    if (EPI != E_STORE && drop.thresh != 0u) o4 = dropout4(o4, drop, r * ldc + n0);
+    st4(C + r * ldc + n0, o4);  // ldc % 4 == 0, n0 % 4 == 0
   }
 }
 
@@ -114,6 +117,7 @@ template <int YMODE, int ACT, bool PREACT>
 __global__ void __launch_bounds__(DW_THREADS)
 k_simt_dw(const float* __restrict__ X, int ldx, AOperand Y, float* __restrict__ P, int64_t R,
           int N1, int N2, int64_t rows_per_chunk) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   __shared__ float Xs[DW_BK][DW_BM + 4];
   __shared__ float Ys[DW_BK][DW_BN + 4];
   const int tid = threadIdx.x;
@@ -174,6 +178,7 @@ k_simt_dw(const float* __restrict__ X, int ldx, AOperand Y, float* __restrict__ 
 // column sums over a row chunk: P[z][n] = sum_{r in chunk z} X[r, n]   (bias gradients)
 __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __restrict__ P,
                                  int64_t R, int N, int64_t rows_per_chunk) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   int64_t r_begin = (int64_t)blockIdx.y * rows_per_chunk, r_end = min(R, r_begin + rows_per_chunk);
@@ -190,6 +195,7 @@ __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __
 // out[i] = sum_z P[z][i] in ascending z (fixed order => bitwise reproducible)
 __global__ void k_reduce_partials(const float* __restrict__ P, float* __restrict__ out, int64_t n,
                                   int Z) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float s = 0.f;

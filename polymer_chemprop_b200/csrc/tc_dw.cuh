@@ -46,6 +46,7 @@ __device__ __forceinline__ float tc_dw_y(const TcDwParams& p, const TcDwTile& t,
 
 template <int YMODE, int ACT, bool PREACT>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_tc_dw(const TcDwParams p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);

@@ -53,6 +53,7 @@ inline int d2_smem_bytes(int maxBN, int nsrc, int raw_stages) {
 
 template <int NSRC, int ACT, bool PREACT>
 __global__ void __launch_bounds__(D2_THREADS, 1) k_tc_dw2(const D2Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);

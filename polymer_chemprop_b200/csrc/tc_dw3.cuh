@@ -80,6 +80,7 @@ __device__ __forceinline__ void d3_store_piece(uint8_t* stage, int r, int c, flo
 
 template <int NSRC, int ACT, bool PREACT>
 __global__ void __launch_bounds__(D3_THREADS, 1) k_tc_dw3(const D3Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);

@@ -107,6 +107,7 @@ __device__ __forceinline__ void d4_epilogue(uint32_t tmem_acc, int we, int lane,
 
 template <int NSRC, int ACT, bool PREACT>
 __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);

@@ -53,6 +53,7 @@ inline int d5_smem_bytes(int XB, int YB, int nsrc, int stages) {
 
 template <int NSRC, int ACT, bool PREACT>
 __global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_constant__ D5Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   constexpr int BK = d5_bk(NSRC), BLK = BK * 128;                             // bytes of one 32-column block
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

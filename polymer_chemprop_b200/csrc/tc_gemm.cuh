@@ -65,6 +65,7 @@ inline int tc_smem_bytes(int BN, int stages) {
 // ---------------------------------------------------------------------------------------------
 __global__ void k_tc_pack_b(const float* __restrict__ W, int ldb, int bmode, int N, int K1, int K2, int BN,
                             int n_tiles, int KC1, int KC, float* __restrict__ Bp) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t total = (int64_t)n_tiles * KC * BN * 32;
   if (e >= total) return;
@@ -194,6 +195,7 @@ __device__ __forceinline__ void tc_epilogue(uint32_t tmem_acc, int we, int lane,
 
 template <int AMODE, int EPI, int ACT, bool PREACT>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_tc_gemm(const TcGemmParams p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);

@@ -79,7 +79,8 @@ inline int t2_smem_bytes(int BN) {
 template <int EPI, int ACT>
 __device__ __forceinline__ void t2_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T2Barriers* bar,
                                             uint32_t& rit, int BN, int64_t row0, int64_t M, int col0, int N, int cmax,
-                                            const float* bias, float* C, int ldc, long long* tacc) {
+                                            const float* bias, float* C, int ldc, long long* tacc,
+                                            const Dropout& drop) {
   for (int c0 = 0; c0 < BN; c0 += 32, ++rit) {
     const int slot = rit % T2_R_SLOTS;
     uint8_t* sl = rring + slot * T2_R_SLOT_BYTES + (we * 32) * T2_R_ROW;     // this warp's 32 rows
@@ -125,6 +126,7 @@ __device__ __forceinline__ void t2_epilogue(uint32_t tmem_acc, int we, int lane,
     for (int i = 0; i < 8; ++i) {
       float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
       if (EPI != E_STORE) x = f4_act<ACT>(x);
+      if (EPI != E_STORE && drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
       const bool ok = in_c && row0 + we * 32 + rq + 4 * i < M && !(WD_ABL & 4);
       if (ok) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
@@ -157,10 +159,12 @@ struct T2Params {
   int N, BN, n_tiles;
   float* S;             // optional copy of the virtual A operand (segment 0, before rounding), [M, lds]
   int lds;
+  Dropout drop;         // applied after the activation (EPI != E_STORE)
 };
 
 template <int NSRC, int EPI, int ACT, bool PREACT>
 __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);
@@ -413,7 +417,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
       T2_WAIT(7, &bar->tmem_full[acc], (tl / nacc) & 1);
       ptx::tc_fence_after();
       t2_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, bar, rit, p.BN, row0, p.M, col0, p.N, p.ldc,
-                            p.bias, p.C, p.ldc, tacc);
+                            p.bias, p.C, p.ldc, tacc, p.drop);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);

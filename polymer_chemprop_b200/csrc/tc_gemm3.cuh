@@ -35,6 +35,7 @@ struct T3Params {
   int ldc;
   int64_t M;
   int N, BN, n_tiles;
+  Dropout drop;         // applied after the activation (EPI == E_ACT)
 };
 
 inline int t3_smem_bytes(int BN) {
@@ -43,6 +44,7 @@ inline int t3_smem_bytes(int BN) {
 
 template <int EPI, int ACT>
 __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constant__ T3Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   static_assert(EPI != E_RES_ACT, "the residual epilogue belongs to the gathered kernel");
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -116,7 +118,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
       T2_WAIT(7, &bar->tmem_full[acc], (tl >> 1) & 1);
       ptx::tc_fence_after();
       t2_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, ebar, rit, p.BN, row0, p.M, col0, p.N, p.ldc,
-                            p.bias, p.C, p.ldc, tacc);
+                            p.bias, p.C, p.ldc, tacc, p.drop);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);

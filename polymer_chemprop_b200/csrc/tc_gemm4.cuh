@@ -55,6 +55,7 @@ struct T4Params {
   int N, BN, n_tiles;
   float* S;             // optional copy of the operand rows, [M, lds]
   int lds;
+  Dropout drop;         // applied after the activation
 };
 
 inline int t4_smem_bytes(int BN) {
@@ -67,7 +68,8 @@ inline int t4_smem_bytes(int BN) {
 template <int ACT>
 __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T4Barriers* bar,
                                             uint32_t& rit, int W, int64_t row0, int64_t M, int col0, int N, int cmax,
-                                            const float* bias, float* C, int ldc, long long* tacc) {
+                                            const float* bias, float* C, int ldc, long long* tacc,
+                                            const Dropout& drop) {
   for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
     const int slot = rit % T4_R_SLOTS;
     uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
@@ -112,6 +114,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     for (int i = 0; i < 8; ++i) {
       float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
       x = f4_act<ACT>(x);
+      if (drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
       if (in_c && row0 + we * 32 + rq + 4 * i < M) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
     }
@@ -123,6 +126,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
 
 template <int ACT, bool PREACT>
 __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constant__ T4Params p) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);
@@ -321,7 +325,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         T2_WAIT(7, &bar->tmem_full[buf], (g / 3) & 1);
         ptx::tc_fence_after();
         t4_epilogue<ACT>(tmem_base + buf * T4_HALF, warp, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
-                         col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc);
+                         col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop);
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[buf]);

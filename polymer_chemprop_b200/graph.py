@@ -30,7 +30,7 @@ class MolGraphData:
 
     __slots__ = ("n_atoms", "n_bonds", "f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a",
                  "b2revb", "degree_of_polym", "overwrite_default_atom_features",
-                 "overwrite_default_bond_features")
+                 "overwrite_default_bond_features", "_prefix_ok")
 
     def __init__(self, f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, degree_of_polym=1):
         self.f_atoms = np.asarray(f_atoms, dtype=np.float32)
@@ -49,6 +49,23 @@ class MolGraphData:
         self.degree_of_polym = degree_of_polym
         self.overwrite_default_atom_features = False
         self.overwrite_default_bond_features = False
+        self._prefix_ok = None
+
+    @property
+    def bond_rows_start_with_atom_row(self) -> bool:
+        """True iff f_bonds[b, :F_a] == f_atoms[b2a[b]] bit for bit for every bond -- how MolGraph builds
+        its bond rows (featurization.py:467-468, :616-629).  Checked exactly, once per molecule."""
+        if self._prefix_ok is None:
+            fa = self.f_atoms.shape[1]
+            if self.n_bonds == 0:
+                self._prefix_ok = True
+            elif self.n_atoms == 0 or self.f_bonds.shape[1] < fa:
+                self._prefix_ok = False
+            else:
+                a = self.f_bonds[:, :fa].view(np.uint32)
+                b = self.f_atoms[self.b2a].view(np.uint32)
+                self._prefix_ok = bool(np.array_equal(a, b))
+        return self._prefix_ok
 
     def as_reference_lists(self):
         """Duck-typed object with plain Python lists, consumable by the *reference's*
@@ -114,6 +131,11 @@ class BatchMolGraph:
                 b2a[b0:b0 + g.n_bonds] = g.b2a + a0
                 b2revb[b0:b0 + g.n_bonds] = g.b2revb + b0
 
+        # Compact form of f_bonds for the upload (csrc/features.cu): when every molecule's bond rows start with
+        # the source atom's row -- verified above, molecule by molecule -- only the bond-only tail is new data.
+        self.f_bonds_tail = None
+        if self.bond_fdim > self.atom_fdim and all(g.bond_rows_start_with_atom_row for g in mol_graphs):
+            self.f_bonds_tail = torch.from_numpy(np.ascontiguousarray(f_bonds[:, self.atom_fdim:]))
         self.f_atoms = torch.from_numpy(f_atoms)
         self.f_bonds = torch.from_numpy(f_bonds)
         self.w_atoms = torch.from_numpy(w_atoms)
@@ -150,8 +172,10 @@ class BatchMolGraph:
     def to(self, device, pin: bool = False) -> "BatchMolGraph":
         """Moves the seven tensors to ``device`` in place (extension over the reference:
         keeps batches resident so mpn.py:84-87's per-call upload disappears)."""
-        for name in ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a", "b2revb"):
+        for name in ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a", "b2revb", "f_bonds_tail"):
             t = getattr(self, name)
+            if t is None:
+                continue
             if pin and t.device.type == "cpu":
                 t = t.pin_memory()
             setattr(self, name, t.to(device, non_blocking=True))

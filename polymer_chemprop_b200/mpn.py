@@ -50,15 +50,33 @@ class DeviceGraph:
         f32 = dict(device=device, dtype=torch.float32, non_blocking=non_blocking)
         i64 = dict(device=device, dtype=torch.int64, non_blocking=non_blocking)
         self.device = device
-        self.f_atoms = self._padded_rows(f_atoms.to(**f32))    # mpn.py:84-87
-        self.f_bonds = self._padded_rows(f_bonds.to(**f32))
+        tail = getattr(mol_graph, "f_bonds_tail", None)
+        self.atom_fdim, self.bond_fdim = f_atoms.shape[1], f_bonds.shape[1]
         self.w_atoms = w_atoms.to(**f32).contiguous()
         self.w_bonds = w_bonds.to(**f32).contiguous()
         a2b = a2b.to(**i64).contiguous()
         b2a = b2a.to(**i64).contiguous()
         b2revb = b2revb.to(**i64).contiguous()
+        self.compact_upload = (tail is not None and f_bonds.device.type == "cpu" and
+                               tail.shape == (f_bonds.shape[0], self.bond_fdim - self.atom_fdim))
+        if self.compact_upload:
+            # f_bonds[b] = [f_atoms[b2a[b]], tail[b]] (featurization.py:467-468): upload f_atoms + the bond-only
+            # tail and rebuild both padded matrices in HBM (wd_expand_features) -- 65 MB instead of 209 MB at B=4096
+            fa_dense = f_atoms.to(**f32).contiguous()
+            tail_d = tail.to(**f32).contiguous()
+            ld_a, ld_b = (self.atom_fdim + 3) // 4 * 4, (self.bond_fdim + 3) // 4 * 4
+            self.f_atoms = torch.empty((fa_dense.shape[0], ld_a), dtype=torch.float32, device=device)
+            self.f_bonds = torch.empty((tail_d.shape[0], ld_b), dtype=torch.float32, device=device)
+            _capi.check(_capi.lib().wd_expand_features(
+                _capi.ptr(fa_dense), _capi.ptr(tail_d), _capi.ptr(b2a), fa_dense.shape[0], tail_d.shape[0],
+                self.atom_fdim, self.bond_fdim - self.atom_fdim, _capi.ptr(self.f_atoms), ld_a,
+                _capi.ptr(self.f_bonds), ld_b, _capi.current_stream(device)))
+            self._dense_keepalive = (fa_dense, tail_d)             # read by the kernels still in flight
+        else:
+            self.f_atoms = self._padded_rows(f_atoms.to(**f32))    # mpn.py:84-87
+            self.f_bonds = self._padded_rows(f_bonds.to(**f32))
+            self._dense_keepalive = None
         self.n_atoms, self.n_bonds, self.n_mols = self.f_atoms.shape[0], self.f_bonds.shape[0], len(a_scope)
-        self.atom_fdim, self.bond_fdim = f_atoms.shape[1], f_bonds.shape[1]
         if a2b.dim() != 2 or a2b.shape[0] != self.n_atoms:
             raise ValueError("a2b must be [n_atoms, max_num_bonds]")
         scope = np.asarray(a_scope, dtype=np.int64).reshape(-1, 2)
@@ -131,6 +149,7 @@ class DeviceGraph:
         self.ready.synchronize()
         self._int64_keepalive = None
         self._host_keepalive = None
+        self._dense_keepalive = None
         if self._validate and int(self.flags_host[0]) != 0:
             raise ValueError(f"inconsistent BatchMolGraph: {int(self.flags_host[0])} invariant violations "
                              "(bond id out of range, bond listed in 0 or >1 a2b rows, b2revb not an involution, "
@@ -164,9 +183,8 @@ class _EncoderFunction(torch.autograd.Function):
     """forward = wd_encoder_forward, backward = wd_encoder_backward (deterministic)."""
 
     @staticmethod
-    def forward(ctx, enc, dg, W_i, b_i, W_h, b_h, W_o, b_o):
+    def forward(ctx, enc, dg, cfg, W_i, b_i, W_h, b_h, W_o, b_o):
         dev = dg.device
-        cfg = enc._config(dg)
         ws_bytes = _capi.lib().wd_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
         if ws_bytes == 0:
             _capi.check(_capi.WD_ERR_INVALID_ARG)
@@ -198,7 +216,7 @@ class _EncoderFunction(torch.autograd.Function):
         ctx.ws = None
         if enc.depth == 1:          # W_h is unused by the reference's graph when depth == 1
             gW_h, gb_h = None, None
-        return None, None, gW_i, gb_i, gW_h, gb_h, gW_o, gb_o
+        return None, None, None, gW_i, gb_i, gW_h, gb_h, gW_o, gb_o
 
 
 class MPNEncoder(nn.Module):
@@ -241,18 +259,38 @@ class MPNEncoder(nn.Module):
         self.W_o = nn.Linear(self.atom_fdim + self.hidden_size, self.hidden_size)
 
     def _config(self, dg: DeviceGraph) -> _capi.WdConfig:
+        """WdConfig of THIS call.  nn.Dropout semantics (mpn.py:38, :124, :134): active only in training mode;
+        a fresh 64-bit Philox key is drawn from torch's CPU generator per call (so torch.manual_seed makes runs
+        repeatable) and the same cfg object goes to the backward call, which regenerates the masks."""
+        p, lo, hi = 0.0, 0, 0
+        if self.training and self.dropout > 0.0:
+            p = float(self.dropout)
+            lo, hi = (int(x) & 0xFFFFFFFF for x in torch.randint(0, 2 ** 32, (2,), dtype=torch.int64).tolist())
         return _capi.WdConfig(self.hidden_size, dg.atom_fdim, dg.bond_fdim, self.depth,
                               _capi.ACTIVATIONS[self.activation], _capi.AGGREGATIONS[self.aggregation],
                               int(bool(self.undirected)), int(bool(self.bias)),
-                              _capi.MATH_MODES[self.math_mode], float(self.aggregation_norm))
+                              _capi.MATH_MODES[self.math_mode], float(self.aggregation_norm), p, lo, hi)
+
+    def _infer(self, dg: DeviceGraph, cfg: _capi.WdConfig) -> torch.Tensor:
+        """Forward only (torch.no_grad(): chemprop/train/predict.py:10-68, molecule_fingerprint.py:151-183):
+        wd_encoder_infer keeps nothing for a backward pass, so the workspace is a third of the training one."""
+        L, dev = _capi.lib(), dg.device
+        ws_bytes = L.wd_infer_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
+        if ws_bytes == 0:
+            _capi.check(_capi.WD_ERR_INVALID_ARG)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        out = torch.empty((dg.n_mols, self.hidden_size), dtype=torch.float32, device=dev)
+        ws_c = [t.detach().contiguous() if t is not None else None
+                for t in (self.W_i.weight, self.W_i.bias, self.W_h.weight, self.W_h.bias, self.W_o.weight, self.W_o.bias)]
+        weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
+        _capi.check(L.wd_encoder_infer(C.byref(dg.struct), C.byref(weights), C.byref(cfg), _capi.ptr(ws), ws_bytes,
+                                       _capi.ptr(out), _capi.current_stream(dev)))
+        return out
 
     def forward(self, mol_graph, atom_descriptors_batch: List[np.ndarray] = None) -> torch.Tensor:
         """Encodes a batch of molecular graphs -> [num_molecules, hidden_size] (mpn.py:66-173)."""
         if atom_descriptors_batch is not None:
             raise NotImplementedError("atom descriptors are not accelerated by the B200 encoder")
-        if self.training and self.dropout > 0.0:
-            raise NotImplementedError("dropout > 0 in training mode is not implemented in the B200 encoder "
-                                      "(the reference's RNG stream cannot be matched); use dropout=0")
         device = self.W_i.weight.device
         if device.type != "cuda":
             raise RuntimeError("the B200 encoder runs on CUDA devices only (no CPU fallback); "
@@ -263,8 +301,12 @@ class MPNEncoder(nn.Module):
         if dg.atom_fdim != self.atom_fdim or dg.bond_fdim != self.bond_fdim:
             raise ValueError(f"feature dims of the batch ({dg.atom_fdim}, {dg.bond_fdim}) do not match the "
                              f"encoder ({self.atom_fdim}, {self.bond_fdim})")
-        return _EncoderFunction.apply(self, dg, self.W_i.weight, self.W_i.bias, self.W_h.weight,
-                                      self.W_h.bias, self.W_o.weight, self.W_o.bias)
+        cfg = self._config(dg)
+        self.last_config = cfg                  # introspection (tests read the dropout key of the call)
+        params = (self.W_i.weight, self.W_i.bias, self.W_h.weight, self.W_h.bias, self.W_o.weight, self.W_o.bias)
+        if not torch.is_grad_enabled() or not any(p is not None and p.requires_grad for p in params):
+            return self._infer(dg, cfg)
+        return _EncoderFunction.apply(self, dg, cfg, *params)
 
 
 def _default_math_mode() -> str:

@@ -3,7 +3,8 @@ import types
 
 import torch
 
-from polymer_chemprop_b200 import BatchMolGraph, MPN
+import _golden
+from polymer_chemprop_b200 import BatchMolGraph, MPN, synth
 
 
 def make_args(hidden_size=300, depth=3, bias=False, dropout=0.0, activation="ReLU", undirected=False,
@@ -44,3 +45,45 @@ def run_fwd_bwd(model, graph, d_out):
     out.backward(d_out.to(out.device))
     grads = {k: p.grad.detach().cpu() for k, p in model.encoder[0].named_parameters() if p.grad is not None}
     return out.detach().cpu(), grads
+
+
+def dropout_case(math_mode, hidden, depth, activation, p, out_tol, grad_tol):
+    """Training-mode dropout against the oracle run with the same Philox masks (GPU tests only)."""
+    from oracle import mpn_oracle
+    graphs = synth.make_graphs("copolymer", 40, 31, dense_features=True, random_edge_weights=True)
+    bmg = BatchMolGraph(graphs + [synth.empty_graph()])
+    torch.manual_seed(5)
+    model = MPN(make_args(hidden_size=hidden, depth=depth, activation=activation, dropout=p,
+                                      wd_math_mode=math_mode), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(torch.device('cuda', 0))
+    for q in model.parameters():
+        if q.requires_grad:
+            torch.nn.init.normal_(q, 0.0, 0.1) if q.dim() == 1 else torch.nn.init.xavier_normal_(q)
+    d_out = torch.randn(len(bmg.a_scope), hidden, generator=torch.Generator().manual_seed(9))
+    enc = model.encoder[0]
+    weights = {k: v.detach().cpu() for k, v in enc.state_dict().items() if k != "cached_zero_vector"}
+    model.train()
+    out, grads = run_fwd_bwd(model, bmg, d_out)
+    cfg = enc.last_config
+    assert abs(cfg.dropout - p) < 1e-7
+    drop = dict(p=p, seed_lo=cfg.dropout_seed_lo, seed_hi=cfg.dropout_seed_hi, ld=(hidden + 7) // 8 * 8)
+    ref_out, ref_grads = mpn_oracle.encoder_forward_backward(bmg.get_components(), weights, d_out, depth=depth,
+                                                             activation=activation, dropout=drop)
+    assert _golden.rel_err(out, ref_out) <= out_tol
+    for k, ref in ref_grads.items():
+        assert _golden.rel_err(grads[k], ref) <= grad_tol, k
+    # a second training call draws a new key; eval() switches dropout off (nn.Dropout semantics, mpn.py:38)
+    out2, _ = run_fwd_bwd(model, bmg, d_out)
+    assert (enc.last_config.dropout_seed_lo, enc.last_config.dropout_seed_hi) != (drop["seed_lo"], drop["seed_hi"])
+    assert not torch.equal(out, out2)
+    model.eval()
+    out_eval, grads_eval = run_fwd_bwd(model, bmg, d_out)
+    ref_eval, ref_grads_eval = mpn_oracle.encoder_forward_backward(bmg.get_components(), weights, d_out, depth=depth,
+                                                                   activation=activation)
+    assert enc.last_config.dropout == 0.0 and _golden.rel_err(out_eval, ref_eval) <= out_tol
+    # the same torch seed reproduces the same masks
+    model.train()
+    torch.manual_seed(77)
+    a, _ = run_fwd_bwd(model, bmg, d_out)
+    torch.manual_seed(77)
+    b, _ = run_fwd_bwd(model, bmg, d_out)
+    assert torch.equal(a, b)

@@ -46,3 +46,27 @@ def test_synthetic_shapes():
     assert torch.equal(bmg.f_bonds[:, :133], bmg.f_atoms[bmg.b2a])
     q = BatchMolGraph(synth.make_graphs("qm9", 200, 0))
     assert q.max_num_bonds <= 4 and 7 <= (q.n_atoms - 1) / 200 <= 9
+
+
+def test_bond_tail_only_when_prefix_property_holds():
+    """BatchMolGraph.f_bonds_tail (the compact upload form, csrc/features.cu) exists iff every molecule's bond
+    rows start with the source atom's row bit for bit (featurization.py:467-468 builds them that way)."""
+    from polymer_chemprop_b200 import synth
+    graphs = synth.make_graphs("copolymer", 20, 7, dense_features=True) + [synth.empty_graph()] + \
+        synth.make_graphs("qm9", 5, 8)
+    bmg = BatchMolGraph(graphs)
+    assert bmg.f_bonds_tail is not None and bmg.f_bonds_tail.is_contiguous()
+    assert torch.equal(bmg.f_bonds_tail, bmg.f_bonds[:, bmg.atom_fdim:])
+    assert torch.equal(torch.cat([bmg.f_atoms[bmg.b2a], bmg.f_bonds_tail], dim=1), bmg.f_bonds)
+    bad = synth.make_graphs("copolymer", 3, 9)
+    bad[1].f_bonds = bad[1].f_bonds.copy()
+    bad[1].f_bonds[2, 5] += 1.0                                   # one bond row no longer repeats its atom row
+    assert BatchMolGraph(bad).f_bonds_tail is None
+    neg0 = synth.make_graphs("copolymer", 2, 10)
+    neg0[0].f_bonds = neg0[0].f_bonds.copy()
+    neg0[0].f_atoms = neg0[0].f_atoms.copy()
+    a = int(neg0[0].b2a[0])
+    col = int(np.argmin(neg0[0].f_atoms[a]))                      # a 0.0 entry: -0.0 == 0.0 numerically, not bitwise
+    assert neg0[0].f_atoms[a, col] == 0.0
+    neg0[0].f_bonds[0, col] = -0.0
+    assert BatchMolGraph(neg0).f_bonds_tail is None

@@ -60,6 +60,30 @@ def test_csr_rejects_inconsistent_graph():
         DeviceGraph(_util.ComponentsGraph(tuple(comps)), DEV).check()
 
 
+def test_compact_upload_rebuilds_features_bit_exactly():
+    """wd_expand_features: f_atoms + the bond-only tail uploaded, f_bonds rebuilt in HBM == the full upload."""
+    graphs = synth.make_graphs("copolymer", 300, 11, dense_features=True) + [synth.empty_graph()] + \
+        synth.make_graphs("qm9", 100, 12)
+    bmg = BatchMolGraph(graphs)
+    assert bmg.f_bonds_tail is not None
+    compact = DeviceGraph(bmg, DEV)
+    full = DeviceGraph(_util.ComponentsGraph(bmg.get_components()), DEV)
+    assert compact.compact_upload and not full.compact_upload
+    for name in ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "in_ptr", "in_idx", "out_idx", "src", "rev", "dst", "mol_of"):
+        a, b = getattr(compact, name), getattr(full, name)
+        assert a.shape == b.shape and torch.equal(a.view(torch.int32), b.view(torch.int32)), name
+    assert torch.equal(compact.f_bonds[:, :bmg.bond_fdim].cpu(), bmg.f_bonds)
+    assert torch.equal(compact.f_atoms[:, :bmg.atom_fdim].cpu(), bmg.f_atoms)
+    # a stream-ordered build (the data-loader path) gives the same bytes
+    side = torch.cuda.Stream(device=DEV)
+    hg = _util.ComponentsGraph(tuple(x.pin_memory() if torch.is_tensor(x) else x for x in bmg.get_components()))
+    hg.f_bonds_tail = bmg.f_bonds_tail.pin_memory()
+    pre = DeviceGraph.prefetch(hg, DEV, side)
+    pre.use_on(torch.cuda.current_stream(DEV))
+    pre.check()
+    assert pre.compact_upload and torch.equal(pre.f_bonds, full.f_bonds) and torch.equal(pre.f_atoms, full.f_atoms)
+
+
 @pytest.mark.parametrize("name", _golden.NAMES)
 def test_encoder_matches_reference_golden_fp32(name):
     g = _golden.load(name)
@@ -161,3 +185,34 @@ def test_full_size_properties_b4096():
     _, g2 = _util.run_fwd_bwd(model, bmg, d2)
     for k in g:
         assert _golden.rel_err(g1[k] + g2[k], g[k]) <= 1e-5, k
+
+
+@pytest.mark.parametrize("hidden,depth,activation,p", [(76, 4, "ReLU", 0.3), (300, 3, "tanh", 0.15), (44, 2, "ELU", 0.5)])
+def test_dropout_matches_oracle_with_the_same_philox_masks_fp32(hidden, depth, activation, p):
+    """Training-mode dropout (mpn.py:124, :134): the reference's RNG stream cannot be shared with a CUDA kernel, so
+    the oracle applies the product's Philox masks (pinned by Random123's known answers, and its op placement by the
+    live reference: tests/test_oracle_vs_reference.py); forward and backward then agree to the FP32 tolerances."""
+    _util.dropout_case("fp32", hidden, depth, activation, p, OUT_TOL, GRAD_TOL)
+
+
+def test_inference_path_equals_training_forward_bitwise():
+    """torch.no_grad() -> wd_encoder_infer (predict.py:10-68): same kernels, smaller workspace, same bits."""
+    import ctypes as C
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 300, 41) + [synth.empty_graph()])
+    for mode in ("fp32", "tf32"):
+        torch.manual_seed(3)
+        model = _util.MPN(_util.make_args(hidden_size=300, depth=4, wd_math_mode=mode), atom_fdim=bmg.atom_fdim,
+                          bond_fdim=bmg.bond_fdim).to(DEV)
+        out_train = model([bmg])
+        assert out_train.requires_grad
+        with torch.no_grad():
+            out_inf = model([bmg])
+        assert not out_inf.requires_grad and torch.equal(out_train.detach(), out_inf)
+        for q in model.parameters():                      # frozen encoder (model.py:49-55) takes the same path
+            q.requires_grad_(False)
+        assert torch.equal(model([bmg]), out_inf)
+        cfg = model.encoder[0].last_config
+        lib = _capi.lib()
+        full = lib.wd_workspace_bytes(C.byref(cfg), bmg.n_atoms, bmg.n_bonds, len(bmg.a_scope))
+        small = lib.wd_infer_workspace_bytes(C.byref(cfg), bmg.n_atoms, bmg.n_bonds, len(bmg.a_scope))
+        assert 0 < small < 0.45 * full

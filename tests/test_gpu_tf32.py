@@ -136,3 +136,9 @@ def test_tf32_full_size_b4096_close_to_fp32_path():
     assert _golden.rel_err(outs["tf32"][0], outs["fp32"][0]) <= OUT_TOL
     for k, ref in outs["fp32"][1].items():
         assert _golden.rel_err(outs["tf32"][1][k], ref) <= GRAD_TOL, k
+
+
+@pytest.mark.parametrize("hidden,depth,p", [(300, 3, 0.2), (96, 4, 0.4)])
+def test_dropout_tf32_matches_oracle_with_the_same_philox_masks(hidden, depth, p):
+    """Dropout in the tcgen05 epilogues (k_tc_gemm4 depth step, k_tc_gemm3 / k_tc_gemm2 atom update)."""
+    _util.dropout_case("tf32", hidden, depth, "ReLU", p, OUT_TOL, GRAD_TOL)

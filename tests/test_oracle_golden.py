@@ -65,3 +65,23 @@ def test_tf32_error_model(name):
     assert _golden.rel_err(out, g["out"]) <= 1e-3
     for k, ref in g["grads"].items():
         assert _golden.rel_err(grads[k], ref) <= 3e-2, k
+
+
+def test_philox_known_answers():
+    """Random123's published known-answer vectors for Philox4x32-10 pin the generator behind the product's
+    dropout masks (csrc/common.cuh philox4x32_10 == oracle/mpn_oracle.py philox4x32_10)."""
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        got = mpn_oracle.philox4x32_10(*[[c] for c in ctr], *key)
+        assert tuple(int(x[0]) for x in got) == want
+
+
+def test_dropout_multiplier_statistics():
+    m = mpn_oracle.dropout_multiplier(2000, 300, 304, 0.25, 7, 9, 2)
+    assert m.shape == (2000, 300) and set(torch.unique(m).tolist()) == {0.0, float(np.float32(1) / np.float32(0.75))}
+    assert abs(float((m == 0).float().mean()) - 0.25) < 5e-3
+    assert not torch.equal(m, mpn_oracle.dropout_multiplier(2000, 300, 304, 0.25, 7, 9, 3))   # sites differ
+    assert torch.equal(mpn_oracle.dropout_multiplier(4, 300, 304, 0.0, 7, 9, 2), torch.ones(4, 300))

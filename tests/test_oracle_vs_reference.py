@@ -41,3 +41,78 @@ def test_oracle_equals_live_reference(kind, n, cfg):
     for k, p in enc.named_parameters():
         if p.grad is not None:
             assert _golden.rel_err(o_grads[k], p.grad) <= 1e-5, k
+
+
+class _MaskedDropout(torch.nn.Module):
+    """Stand-in for the reference's nn.Dropout whose k-th call multiplies by the k-th given mask: shares the
+    product's Philox masks with the UNMODIFIED reference forward so that the oracle's dropout placement
+    (mpn.py:124 after every message update, :134 after the atom update) is pinned against it."""
+
+    def __init__(self, multipliers):
+        super().__init__()
+        self.multipliers, self.calls = multipliers, 0
+
+    def forward(self, x):
+        m = self.multipliers[self.calls]
+        self.calls += 1
+        return x * m
+
+
+def test_oracle_dropout_placement_equals_live_reference():
+    ref = ref_shim.load_reference()
+    graphs = synth.make_graphs("copolymer", 6, seed=3, dense_features=True, random_edge_weights=True)
+    ref_bmg, ours_bmg = ref.BatchMolGraph(graphs), BatchMolGraph(graphs)
+    h, depth, p, lo, hi = 48, 4, 0.35, 0x1234ABCD, 0x0BADF00D
+    torch.manual_seed(6)
+    model = ref.MPN(ref_shim.make_args(hidden_size=h, depth=depth, dropout=p), atom_fdim=ours_bmg.atom_fdim,
+                    bond_fdim=ours_bmg.bond_fdim)
+    for q in model.parameters():
+        if q.requires_grad:
+            torch.nn.init.normal_(q, 0.0, 0.1) if q.dim() == 1 else torch.nn.init.xavier_normal_(q)
+    enc = model.encoder[0]
+    ld = (h + 7) // 8 * 8
+    n_b, n_a = ours_bmg.n_bonds, ours_bmg.n_atoms
+    masks = [mpn_oracle.dropout_multiplier(n_b, h, ld, p, lo, hi, t) for t in range(1, depth)] + \
+            [mpn_oracle.dropout_multiplier(n_a, h, ld, p, lo, hi, depth)]
+    assert 0.25 < float((masks[0] == 0).float().mean()) < 0.45
+    enc.dropout_layer = _MaskedDropout(masks)
+    model.train()
+    out = model([ref_bmg])
+    assert enc.dropout_layer.calls == depth
+    d_out = torch.randn(out.shape, generator=torch.Generator().manual_seed(4))
+    out.backward(d_out)
+    weights = {k: v.detach() for k, v in enc.state_dict().items() if k != "cached_zero_vector"}
+    o_out, o_grads = mpn_oracle.encoder_forward_backward(
+        ours_bmg.get_components(), weights, d_out, depth=depth,
+        dropout=dict(p=p, seed_lo=lo, seed_hi=hi, ld=ld))
+    assert _golden.rel_err(o_out, out.detach()) <= 1e-6
+    for k, q in enc.named_parameters():
+        if q.grad is not None:
+            assert _golden.rel_err(o_grads[k], q.grad) <= 1e-5, k
+
+
+def test_install_makes_the_reference_model_build_this_encoder():
+    """mpn.install() (INTEGRATION.md): chemprop.models.model.MoleculeModel.create_encoder (model.py:41-47) then
+    instantiates this package's MPN; the reference's checkpoint keys / shapes are unchanged, so its own
+    load_checkpoint (utils.py:98-135) keeps working.  Host logic only -- no GPU compute here."""
+    import importlib
+    from oracle import make_golden_model
+    from polymer_chemprop_b200 import mpn as ours
+    ref_shim.load_reference()
+    cm = importlib.import_module("chemprop.models.model")
+    cmpn = importlib.import_module("chemprop.models.mpn")
+    args = make_golden_model.model_args(hidden_size=64, depth=3, ffn_num_layers=2, ffn_hidden_size=32, num_tasks=2)
+    torch.manual_seed(0)
+    ref_model = cm.MoleculeModel(args)
+    saved = (cm.MPN, cmpn.MPN, cmpn.MPNEncoder)
+    try:
+        ours.install()
+        model = cm.MoleculeModel(args)
+        assert isinstance(model.encoder, ours.MPN) and isinstance(model.encoder.encoder[0], ours.MPNEncoder)
+        assert list(model.state_dict()) == list(ref_model.state_dict())
+        assert all(model.state_dict()[k].shape == v.shape for k, v in ref_model.state_dict().items())
+        model.load_state_dict(ref_model.state_dict())
+        with pytest.raises(RuntimeError, match="no CPU fallback"):      # parameters on the CPU: refuse, never fall back
+            model([BatchMolGraph(synth.make_graphs("qm9", 2, 0))])
+    finally:
+        cm.MPN, cmpn.MPN, cmpn.MPNEncoder = saved
