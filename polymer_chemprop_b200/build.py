@@ -5,6 +5,7 @@ header changed) and the objects are linked into polymer_chemprop_b200/libwdmpnn.
 import glob
 import os
 import subprocess
+import time
 from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -32,9 +33,12 @@ def _stale() -> bool:
 
 
 def _run(cmd):
+    t0 = time.time()
     proc = subprocess.run(cmd, capture_output=True, text=True)
     if proc.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+    if "-c" in cmd:      # stamp the object with the START of its compile: a source edited meanwhile makes it stale
+        os.utime(cmd[cmd.index("-o") + 1], (t0, t0))
     return proc.stderr
 
 

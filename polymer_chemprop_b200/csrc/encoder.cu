@@ -166,7 +166,7 @@ int bind_packed(const WdConfig& c, Layout& L, void* ws) {
 
 int reduce_partials(cudaStream_t s, const float* P, float* out, int64_t n, int Z) {
   ProfScope ps(WD_PROF_REDUCE);
-  WD_LAUNCH(k_reduce_partials, grid1d(n), 256, 0, s, P, out, n, Z);
+  WD_LAUNCH(k_reduce_partials, (unsigned)ceil_div(n, RP_COLS), RP_COLS * RP_GROUPS, 0, s, P, out, n, Z);
   return WD_OK;
 }
 
@@ -181,6 +181,18 @@ int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_
 
 #define WD_TRY(expr) do { int _rc = (expr); if (_rc != WD_OK) return _rc; } while (0)
 
+// out[a] = sum over the in-edge (incoming == true, weighted by w) or out-edge list of atom a of U(b)
+template <int ACT, bool PREACT>
+int aggregate(cudaStream_t s, const WdGraph& g, bool incoming, const float* U, int ld, const float* w, float* out) {
+  const int nc4 = ld / 4;
+  const int64_t Na = g.n_atoms;
+  // (a padded [N_a, K] int32 form of the lists -- one 16-byte id load at a fixed address instead of the ptr -> idx
+  //  chain -- was measured 5 % SLOWER on B200, profiles/r1_j_padded_lists_vs_csr.txt, and removed)
+  WD_LAUNCH((k_aggregate<ACT, PREACT>), grid1d(Na * nc4), 256, 0, s, U, ld, w, g.in_ptr,
+            incoming ? g.in_idx : g.out_idx, out, Na, nc4);
+  return WD_OK;
+}
+
 // ---- forward ----------------------------------------------------------------------------------
 template <int ACT>
 int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, float* out,
@@ -192,9 +204,11 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   bind_packed(c, L, ws);
   if (c.math_mode == WD_MATH_TF32) {   // weights change every step: repack (tiny) on the stream
     ProfScope ps(WD_PROF_MISC);
-    WD_TRY(tc_pack(s, w.W_i, Fb, B_NK, L.pWi));
-    if (c.depth > 1) WD_TRY(tc_pack(s, w.W_h, h, B_NK, L.pWh));
-    WD_TRY(tc_pack(s, w.W_o, Fa + h, B_NK, L.pWo));
+    TcPacker pk;                       // one launch for the three forward weights
+    pk.add(w.W_i, Fb, B_NK, L.pWi);
+    if (c.depth > 1) pk.add(w.W_h, h, B_NK, L.pWh);
+    pk.add(w.W_o, Fa + h, B_NK, L.pWo);
+    WD_TRY(pk.run(s));
   }
   // input = W_i(f_bonds)                                                      mpn.py:96
   AOperand a_in{g.f_bonds, nullptr, nullptr, nullptr, g.ld_bonds ? g.ld_bonds : Fb, 0, 0};
@@ -217,8 +231,8 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     }
     // a_message = sum_k w_bonds[a2b] * message[a2b]                                  :112-118
     { ProfScope ps(WD_PROF_AGGREGATE);
-    if (upre) WD_LAUNCH((k_aggregate<ACT, true>), grid1d(Na * nc4), 256, 0, s, u, ld, g.w_bonds, g.in_ptr, g.in_idx, A_t, Na, nc4);
-    else      WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, u, ld, g.w_bonds, g.in_ptr, g.in_idx, A_t, Na, nc4); }
+    if (upre) WD_TRY((aggregate<ACT, true>(s, g, true, u, ld, g.w_bonds, A_t)));
+    else      WD_TRY((aggregate<ACT, false>(s, g, true, u, ld, g.w_bonds, A_t))); }
     ProfScope ps(WD_PROF_DEPTH_STEP);
     // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
     AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
@@ -232,8 +246,8 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   // final aggregate + atom update                                                    :127-134
   float* A_d = L.p(ws, L.Agg) + (int64_t)(infer ? 0 : c.depth - 1) * L.szA;
   { ProfScope ps(WD_PROF_AGGREGATE);
-  if (c.depth == 1) WD_LAUNCH((k_aggregate<ACT, true>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4);
-  else              WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, prev, ld, g.w_bonds, g.in_ptr, g.in_idx, A_d, Na, nc4); }
+  if (c.depth == 1) WD_TRY((aggregate<ACT, true>(s, g, true, prev, ld, g.w_bonds, A_d)));
+  else              WD_TRY((aggregate<ACT, false>(s, g, true, prev, ld, g.w_bonds, A_d))); }
   float* H = L.p(ws, L.H);
   AOperand a_o{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
   { ProfScope ps(WD_PROF_ATOM_UPDATE);
@@ -274,8 +288,10 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   bind_packed(c, L, ws);
   if (c.math_mode == WD_MATH_TF32) {
     ProfScope ps(WD_PROF_MISC);
-    if (c.depth > 1) WD_TRY(tc_pack(s, w.W_h, h, B_KN, L.pWhT));
-    WD_TRY(tc_pack(s, w.W_o + Fa, Fo, B_KN, L.pWoT));
+    TcPacker pk;                       // one launch for the two transposed backward weights
+    if (c.depth > 1) pk.add(w.W_h, h, B_KN, L.pWhT);
+    pk.add(w.W_o + Fa, Fo, B_KN, L.pWoT);
+    WD_TRY(pk.run(s));
   }
   const int64_t Na = g.n_atoms, Nb = g.n_bonds;
   const int d = c.depth;
@@ -344,7 +360,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     { ProfScope ps(WD_PROF_DX);
     WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_z, w.W_h, h, nullptr, nullptr, 0, dS, ld, Nb, h, h, &L.pWhT))); }
     ProfScope ps(WD_PROF_SCATTER);
-    WD_LAUNCH((k_aggregate<ACT, false>), grid1d(Na * nc4), 256, 0, s, dS, ld, nullptr, g.in_ptr, g.out_idx, dA, Na, nc4);
+    WD_TRY((aggregate<ACT, false>(s, g, false, dS, ld, nullptr, dA)));
   }
   if (d > 1) {
     { ProfScope ps(WD_PROF_DW);

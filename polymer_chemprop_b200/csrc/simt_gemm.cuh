@@ -192,15 +192,35 @@ __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __
   P[(int64_t)blockIdx.y * N + n] = (s0 + s1) + (s2 + s3);
 }
 
-// out[i] = sum_z P[z][i] in ascending z (fixed order => bitwise reproducible)
-__global__ void k_reduce_partials(const float* __restrict__ P, float* __restrict__ out, int64_t n,
-                                  int Z) {
+// out[i] = sum_z P[z][i].  The Z partials are split into RP_GROUPS contiguous ranges summed concurrently
+// (ascending z inside a range, four independent accumulators), then the range sums are added in ascending order:
+// a fixed association order, hence bitwise reproducible; the split keeps 8x more loads in flight than one
+// thread walking all Z partials (Z is ~74..148 at batch 4096).
+constexpr int RP_COLS = 32, RP_GROUPS = 8;
+__global__ void __launch_bounds__(RP_COLS * RP_GROUPS)
+k_reduce_partials(const float* __restrict__ P, float* __restrict__ out, int64_t n, int Z) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  float s = 0.f;
-  for (int z = 0; z < Z; ++z) s += P[(int64_t)z * n + i];
-  out[i] = s;
+  __shared__ float part[RP_GROUPS][RP_COLS];
+  const int tx = threadIdx.x & (RP_COLS - 1), ty = threadIdx.x / RP_COLS;
+  const int64_t i = (int64_t)blockIdx.x * RP_COLS + tx;
+  const int z0 = (int)((int64_t)Z * ty / RP_GROUPS), z1 = (int)((int64_t)Z * (ty + 1) / RP_GROUPS);
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (i < n) {
+    int z = z0;
+    for (; z + 4 <= z1; z += 4) {
+      s0 += P[(int64_t)(z + 0) * n + i]; s1 += P[(int64_t)(z + 1) * n + i];
+      s2 += P[(int64_t)(z + 2) * n + i]; s3 += P[(int64_t)(z + 3) * n + i];
+    }
+    for (; z < z1; ++z) s0 += P[(int64_t)z * n + i];
+  }
+  part[ty][tx] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  if (ty == 0 && i < n) {
+    float s = part[0][tx];
+#pragma unroll
+    for (int g = 1; g < RP_GROUPS; ++g) s += part[g][tx];
+    out[i] = s;
+  }
 }
 
 }  // namespace wd

@@ -63,12 +63,30 @@ inline int tc_smem_bytes(int BN, int stages) {
 // [BN rows x 128 bytes] in SWIZZLE_128B order, tf32-rounded, zero padded.  The K axis is the
 // concatenation of two segments (K1, K2), each padded to a multiple of 32.
 // ---------------------------------------------------------------------------------------------
-__global__ void k_tc_pack_b(const float* __restrict__ W, int ldb, int bmode, int N, int K1, int K2, int BN,
-                            int n_tiles, int KC1, int KC, float* __restrict__ Bp) {
+struct TcPackJob {
+  const float* W;
+  int ldb, bmode, N, K1, K2, BN, n_tiles, KC1, KC;
+  float* Bp;
+  int64_t first;     // index of this job's first element in the launch (jobs are laid end to end)
+};
+struct TcPackJobs {  // up to three weight matrices packed by ONE launch (forward: W_i, W_h, W_o; backward: W_h^T, W_o^T)
+  TcPackJob job[3];
+  int n;
+  int64_t total;
+};
+
+__global__ void k_tc_pack_b(const TcPackJobs jobs) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t total = (int64_t)n_tiles * KC * BN * 32;
-  if (e >= total) return;
+  if (e >= jobs.total) return;
+  int ji = 0;
+  if (jobs.n > 1 && e >= jobs.job[1].first) ji = 1;
+  if (jobs.n > 2 && e >= jobs.job[2].first) ji = 2;
+  const TcPackJob& j = jobs.job[ji];
+  e -= j.first;
+  const float* __restrict__ W = j.W;
+  float* __restrict__ Bp = j.Bp;
+  const int ldb = j.ldb, bmode = j.bmode, N = j.N, K1 = j.K1, K2 = j.K2, BN = j.BN, KC1 = j.KC1, KC = j.KC;
   int kk = (int)(e & 31);
   int nl = (int)((e >> 5) % BN);
   int kc = (int)((e / (32 * (int64_t)BN)) % KC);

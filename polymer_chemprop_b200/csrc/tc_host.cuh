@@ -46,11 +46,25 @@ inline TcPacked tc_packed_geometry(int N, int K1, int K2, int max_bn = T2_MAX_BN
   return g;
 }
 
+// Collects up to three (weight matrix -> packed image) jobs and packs them with one launch.
+struct TcPacker {
+  TcPackJobs jobs{};
+  void add(const float* W, int ldb, int bmode, const TcPacked& g) {
+    TcPackJob& j = jobs.job[jobs.n++];
+    j = TcPackJob{W, ldb, bmode, g.N, g.K1, g.K2, g.BN, g.n_tiles, g.KC1, g.KC, g.img, jobs.total};
+    jobs.total += g.floats();
+  }
+  int run(cudaStream_t s) {
+    if (jobs.n == 0) return WD_OK;
+    WD_LAUNCH(k_tc_pack_b, (unsigned)ceil_div(jobs.total, 256), 256, 0, s, jobs);
+    return WD_OK;
+  }
+};
+
 inline int tc_pack(cudaStream_t s, const float* W, int ldb, int bmode, const TcPacked& g) {
-  const int64_t total = g.floats();
-  WD_LAUNCH(k_tc_pack_b, (unsigned)ceil_div(total, 256), 256, 0, s, W, ldb, bmode, g.N, g.K1, g.K2, g.BN, g.n_tiles,
-            g.KC1, g.KC, g.img);
-  return WD_OK;
+  TcPacker pk;
+  pk.add(W, ldb, bmode, g);
+  return pk.run(s);
 }
 
 inline bool tc_aligned16(const void* p, int ld) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld & 3) == 0; }

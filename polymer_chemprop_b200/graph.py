@@ -104,6 +104,11 @@ class BatchMolGraph:
         self.a_scope: List[Tuple[int, int]] = [(int(s), int(n)) for s, n in zip(a_start, na)]
         self.b_scope: List[Tuple[int, int]] = [(int(s), int(n)) for s, n in zip(b_start, nb)]
         self.degree_of_polym = [g.degree_of_polym for g in mol_graphs]
+        # array forms of a_scope / degree_of_polym for the upload (the 10-tuple keeps the reference's Python lists;
+        # converting 4096 tuples per batch costs milliseconds of host time, more than the encoder step itself)
+        self.a_scope_array = torch.from_numpy(np.concatenate([a_start, na]).astype(np.int32))       # starts | sizes
+        self.dop_array = torch.from_numpy(np.fromiter((float(x) for x in self.degree_of_polym), dtype=np.float32,
+                                                      count=len(mol_graphs)))
 
         f_atoms = np.zeros((self.n_atoms, self.atom_fdim), dtype=np.float32)
         f_bonds = np.zeros((self.n_bonds, self.bond_fdim), dtype=np.float32)
@@ -168,6 +173,25 @@ class BatchMolGraph:
             revmask = (b2b != self.b2revb.unsqueeze(1)).long()
             self.b2b = b2b * revmask
         return self.b2b
+
+    _TENSORS = ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a", "b2revb", "f_bonds_tail", "a_scope_array",
+                "dop_array")
+
+    def pin_memory(self) -> "BatchMolGraph":
+        """Page-locks the host tensors in place (what a DataLoader with pin_memory=True does to its batches), so
+        that DeviceGraph.prefetch can upload them asynchronously on a copy stream."""
+        for name in self._TENSORS:
+            t = getattr(self, name)
+            if t is not None and t.device.type == "cpu" and not t.is_pinned():
+                setattr(self, name, t.pin_memory())
+        return self
+
+    def fresh_view(self) -> "BatchMolGraph":
+        """A new batch object over the same host tensors with nothing cached on it (no device copy)."""
+        import copy
+        other = copy.copy(self)
+        other.__dict__.pop("_wd_cache", None)
+        return other
 
     def to(self, device, pin: bool = False) -> "BatchMolGraph":
         """Moves the seven tensors to ``device`` in place (extension over the reference:

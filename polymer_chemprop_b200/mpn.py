@@ -79,11 +79,16 @@ class DeviceGraph:
         self.n_atoms, self.n_bonds, self.n_mols = self.f_atoms.shape[0], self.f_bonds.shape[0], len(a_scope)
         if a2b.dim() != 2 or a2b.shape[0] != self.n_atoms:
             raise ValueError("a2b must be [n_atoms, max_num_bonds]")
-        scope = np.asarray(a_scope, dtype=np.int64).reshape(-1, 2)
-        host = torch.from_numpy(np.concatenate([scope[:, 0], scope[:, 1]]).astype(np.int32))
-        dop_h = torch.tensor([float(x) for x in dop], dtype=torch.float32)
+        host, dop_h = getattr(mol_graph, "a_scope_array", None), getattr(mol_graph, "dop_array", None)
+        if host is None or dop_h is None or host.numel() != 2 * len(a_scope) or dop_h.numel() != len(a_scope):
+            # a foreign batch object: the reference's Python lists (featurization.py:795-800) are converted here
+            scope = np.fromiter((v for se in a_scope for v in se), dtype=np.int64, count=2 * len(a_scope)).reshape(-1, 2)
+            host = torch.from_numpy(np.concatenate([scope[:, 0], scope[:, 1]]).astype(np.int32))
+            dop_h = torch.from_numpy(np.fromiter((float(x) for x in dop), dtype=np.float32, count=len(dop)))
+        host, dop_h = host.to(torch.int32), dop_h.to(torch.float32)              # no-ops for the cached arrays
         if device.type == "cuda":
-            host, dop_h = host.pin_memory(), dop_h.pin_memory()
+            host = host if host.is_pinned() else host.pin_memory()
+            dop_h = dop_h if dop_h.is_pinned() else dop_h.pin_memory()
         self._host_keepalive = (host, dop_h)                   # pinned sources of in-flight async copies
         scopes = host.to(device, non_blocking=True)
         self.a_start, self.a_size = scopes[:self.n_mols], scopes[self.n_mols:]
