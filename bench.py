@@ -342,6 +342,7 @@ def main():
         host_out = torch.empty(G, a.hidden).pin_memory()
         d2h = host_out.numel() * 4
         copy_stream = torch.cuda.Stream(device=dev)
+        d2h_stream = torch.cuda.Stream(device=dev)
 
         def nbytes(ts):
             return sum(x.numel() * x.element_size() for x in ts)
@@ -366,12 +367,18 @@ def main():
                 for p in params:
                     p.grad = None
                 out = model([cur])
+                fwd_done = torch.cuda.Event()
+                fwd_done.record()
+                with torch.cuda.stream(d2h_stream):      # the result leaves on its own stream while the backward runs
+                    d2h_stream.wait_event(fwd_done)
+                    host_out.copy_(out.detach(), non_blocking=True)
+                out.detach().record_stream(d2h_stream)
                 out.backward(d_out)
                 if world > 1:
                     reducer()
-                host_out.copy_(out.detach(), non_blocking=True)
                 state["next"] = next_batch()             # upload of batch i+1 overlaps the step of batch i
                 torch.cuda.current_stream().synchronize()
+                d2h_stream.synchronize()
 
             for _ in range(3):
                 e2e_step()

@@ -80,6 +80,10 @@ typedef struct WdGraph {
   int32_t ld_atoms;       /* row stride of f_atoms in floats; 0 = F_a (dense, the reference layout) */
   int32_t ld_bonds;       /* row stride of f_bonds in floats; 0 = F_b.  Strides that are multiples   */
                           /* of 4 put the feature rows on the 16-byte asynchronous-copy path         */
+  int32_t rev_adjacent;   /* 1 iff wd_csr_build reported flags[2] == 0: b2revb[b] == ((b-1)^1)+1 for every real bond,  */
+                          /* i.e. reverse bonds are adjacent pairs (how featurization.py:470-480 / :616-629 number     */
+                          /* them).  The gathered depth step then fetches message[b2revb] as plain TMA boxes.  0 is    */
+                          /* always safe (gathered copies).                                                           */
 } WdGraph;
 
 /* nn.Linear layout [out, in] row-major, exactly the reference's parameters (mpn.py:47-57).
@@ -109,7 +113,8 @@ typedef struct WdGrads {
  * a_start / a_size are DEVICE int32 [G]; mol_of [N_a] is filled from them.
  * `flags` is a DEVICE int32[4] written by the kernels: [0] number of invariant violations
  * (bond id out of range, bond listed in 0 or >1 rows, dst != b2a[b2revb], b2revb not an
- * involution, scope out of range), [1] max in-degree seen, [2..3] reserved. */
+ * involution, scope out of range), [1] max in-degree seen, [2] number of real bonds whose reverse is NOT the
+ * adjacent one (b2revb[b] != ((b-1)^1)+1; 0 for every graph the reference builds), [3] reserved. */
 int wd_csr_build(const int64_t* a2b, int64_t n_atoms, int64_t max_num_bonds, const int64_t* b2a,
                  const int64_t* b2revb, int64_t n_bonds, const int32_t* a_start,
                  const int32_t* a_size, int64_t n_mols, int32_t* in_ptr, int32_t* in_idx,

@@ -33,7 +33,7 @@ class WdGraph(C.Structure):
                 ("w_bonds", C.c_void_p), ("in_ptr", C.c_void_p), ("in_idx", C.c_void_p),
                 ("out_idx", C.c_void_p), ("src", C.c_void_p), ("rev", C.c_void_p), ("dst", C.c_void_p),
                 ("mol_of", C.c_void_p), ("a_start", C.c_void_p), ("a_size", C.c_void_p),
-                ("dop", C.c_void_p), ("ld_atoms", C.c_int32), ("ld_bonds", C.c_int32)]
+                ("dop", C.c_void_p), ("ld_atoms", C.c_int32), ("ld_bonds", C.c_int32), ("rev_adjacent", C.c_int32)]
 
 
 class WdWeights(C.Structure):

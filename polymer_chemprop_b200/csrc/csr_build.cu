@@ -132,6 +132,7 @@ __global__ void k_csr_bonds(const int64_t* __restrict__ b2a, const int64_t* __re
     dst[0] = 0;
     if (in_ptr[n_atoms] != (int32_t)(n_bonds - 1)) ++bad;  // every real bond listed exactly once
   } else {
+    if (r != ((b - 1) ^ 1) + 1) atomicAdd(&flags[2], 1);    // not an adjacent reverse pair (never for reference-built graphs)
     if (b2revb[r] != b) ++bad;                              // reverse map is an involution
     int64_t sr = b2a[r];
     if (dst[b] < 0 || dst[b] != (int32_t)sr) ++bad;         // a2b row of b == source of rev(b)

@@ -236,6 +236,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     ProfScope ps(WD_PROF_DEPTH_STEP);
     // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
     AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
+    a_s.rev_adjacent = g.rev_adjacent;
     if (c.math_mode == WD_MATH_TF32 && !tc_use_v1() && !infer) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
     const float* bh = c.bias ? w.b_h : nullptr;
     const Dropout drop = make_dropout(c, t);                                          // :124

@@ -113,6 +113,10 @@ extern "C" int wd_encoder_host(const float* f_atoms, const float* f_bonds, const
   if (rc != WD_OK) return rc;
   rc = wd_csr_build_check(flags, s);
   if (rc != WD_OK) return rc;
+  int32_t h_flags[4] = {0, 0, 1, 0};
+  WD_CUDA_OK(cudaMemcpyAsync(h_flags, flags, sizeof(h_flags), cudaMemcpyDeviceToHost, s));
+  WD_CUDA_OK(cudaStreamSynchronize(s));
+  dg.rev_adjacent = h_flags[2] == 0 ? 1 : 0;
   dg.n_atoms = Na; dg.n_bonds = Nb; dg.n_mols = G;
   dg.f_atoms = d_fa; dg.f_bonds = d_fb; dg.w_atoms = d_wa; dg.w_bonds = d_wb;
   dg.ld_atoms = lda; dg.ld_bonds = ldb;

@@ -21,6 +21,7 @@ struct AOperand {
   const int32_t* src;  // GATHER_DIFF: b2a
   const int32_t* rev;  // GATHER_DIFF: b2revb
   int ldx, ldx2, K1;
+  int rev_adjacent;    // GATHER_DIFF: rev[r] == ((r-1)^1)+1 for every r >= 1 (WdGraph.rev_adjacent): X2 rows can come by TMA
   float* S_out;        // GATHER_DIFF on the tensor-core path: the operand rows X[src] - act?(X2[rev]) are also
                        // written here ([M, ldx2], fp32) so that the weight-gradient pass can read them as a plain matrix
 };

@@ -122,6 +122,12 @@ int tc_gemm4(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   p.Bp = B.img; p.bias = bias; p.C = C; p.ldc = ldc; p.M = M;
   p.N = B.N; p.BN = B.BN; p.n_tiles = B.n_tiles;
   p.S = A.S_out; p.lds = A.ldx2;
+  static const bool x1_tma_off = [] { const char* e = getenv("WD_T4_X1_TMA"); return e && atoi(e) == 0; }();   // A/B runs
+  p.x1_tma = (A.rev_adjacent && A.rev != nullptr && !x1_tma_off) ? 1 : 0;
+  if (p.x1_tma) {
+    rc = tma_make_2d(&p.mx1, A.X2, M, B.K1, A.ldx2, T4_X1_ROWS, TMA_SW128, /*round_tf32=*/false);
+    if (rc != WD_OK) return rc;
+  }
   const int smem = t4_smem_bytes(B.BN);
   if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 tile does not fit shared memory");
   auto kern = k_tc_gemm4<ACT, PREACT>;

@@ -27,6 +27,9 @@ def get_activation_function(activation: str) -> nn.Module:
     return table[activation]()
 
 
+_PINNED_FLAGS = []     # recycled 4-int pinned buffers: a fresh cudaHostAlloc per batch costs ~1 ms of host time
+
+
 class DeviceGraph:
     """Device-resident form of one BatchMolGraph: the get_components() tensors moved once, plus the
     int32 CSR / reverse-CSR arrays rebuilt on the device by wd_csr_build.  Cached on the
@@ -109,8 +112,9 @@ class DeviceGraph:
                                    p(self.in_idx), p(self.out_idx), p(self.src), p(self.rev), p(self.dst),
                                    p(self.mol_of), p(self.flags), stream))
         self._int64_keepalive = (a2b, b2a, b2revb)             # read by the CSR kernels still in flight
-        self.flags_host = torch.empty(4, dtype=torch.int32).pin_memory() if device.type == "cuda" else None
-        if self.flags_host is not None:
+        self.flags_host = None
+        if device.type == "cuda":
+            self.flags_host = _PINNED_FLAGS.pop() if _PINNED_FLAGS else torch.empty(4, dtype=torch.int32).pin_memory()
             self.flags_host.copy_(self.flags, non_blocking=True)
         self.build_stream = torch.cuda.current_stream(device)
         self.ready = torch.cuda.Event()
@@ -155,8 +159,14 @@ class DeviceGraph:
         self._int64_keepalive = None
         self._host_keepalive = None
         self._dense_keepalive = None
-        if self._validate and int(self.flags_host[0]) != 0:
-            raise ValueError(f"inconsistent BatchMolGraph: {int(self.flags_host[0])} invariant violations "
+        flags = self.flags_host.tolist()
+        _PINNED_FLAGS.append(self.flags_host)                  # its copy has completed: hand the buffer on
+        self.flags_host = None
+        self.violations, self.max_in_degree = flags[0], flags[1]
+        self.rev_adjacent = flags[2] == 0                      # reverse bonds are adjacent pairs (featurization.py:470-480)
+        self.struct.rev_adjacent = int(self.rev_adjacent)
+        if self._validate and flags[0] != 0:
+            raise ValueError(f"inconsistent BatchMolGraph: {flags[0]} invariant violations "
                              "(bond id out of range, bond listed in 0 or >1 a2b rows, b2revb not an involution, "
                              "or a_scope out of range)")
         self._checked = True

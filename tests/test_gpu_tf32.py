@@ -142,3 +142,67 @@ def test_tf32_full_size_b4096_close_to_fp32_path():
 def test_dropout_tf32_matches_oracle_with_the_same_philox_masks(hidden, depth, p):
     """Dropout in the tcgen05 epilogues (k_tc_gemm4 depth step, k_tc_gemm3 / k_tc_gemm2 atom update)."""
     _util.dropout_case("tf32", hidden, depth, "ReLU", p, OUT_TOL, GRAD_TOL)
+
+
+def _big_batch():
+    return BatchMolGraph(synth.make_graphs("copolymer", 300, 61, random_edge_weights=True) + [synth.empty_graph()] +
+                         synth.make_graphs("qm9", 50, 62))
+
+
+def _model(bmg, hidden=300, depth=4, mode="tf32", **kw):
+    torch.manual_seed(1)
+    model = _util.MPN(_util.make_args(hidden_size=hidden, depth=depth, wd_math_mode=mode, **kw),
+                      atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)
+    for p in model.parameters():
+        if p.requires_grad and p.dim() == 2:
+            torch.nn.init.xavier_normal_(p)
+    return model
+
+
+@pytest.mark.parametrize("undirected", [False, True])
+def test_reverse_message_tma_box_equals_gathered_rows_bitwise(undirected):
+    """Gathered depth step: message[b2revb] fetched as one TMA box per tile (reverse bonds are adjacent pairs in
+    every reference-built graph, featurization.py:470-480 / :616-629; WdGraph.rev_adjacent) against the gathered
+    cp.async rows -- same arithmetic, so the whole forward and backward must agree bit for bit."""
+    from polymer_chemprop_b200 import DeviceGraph
+    bmg = _big_batch()
+    model = _model(bmg, undirected=undirected)
+    d_out = torch.randn(len(bmg.a_scope), 300, generator=torch.Generator().manual_seed(2))
+    out_tma, grads_tma = _util.run_fwd_bwd(model, bmg, d_out)
+    assert DeviceGraph.get(bmg, DEV).rev_adjacent and DeviceGraph.get(bmg, DEV).struct.rev_adjacent == 1
+    other = bmg.fresh_view()
+    dg = DeviceGraph.get(other, DEV)
+    dg.check()
+    dg.struct.rev_adjacent = 0                                   # force the gathered path
+    out_g, grads_g = _util.run_fwd_bwd(model, other, d_out)
+    assert torch.equal(out_tma, out_g)
+    for k in grads_tma:
+        assert torch.equal(grads_tma[k], grads_g[k]), k
+
+
+def test_renumbered_bonds_take_the_gathered_path_and_match_the_oracle():
+    """A valid BatchMolGraph whose bonds are renumbered at random (reverse pairs no longer adjacent): wd_csr_build
+    reports it (flags[2] > 0), the depth step gathers message[b2revb] row by row, and the result matches the oracle
+    on the renumbered tensors -- and the encoder output of the original numbering (the encoder is invariant under
+    a renumbering of the bonds that keeps every a2b row's order)."""
+    from polymer_chemprop_b200 import DeviceGraph
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 40, 71, dense_features=True, random_edge_weights=True))
+    fa, fb, wa, wb, a2b, b2a, b2revb, a_scope, b_scope, dop = bmg.get_components()
+    n_b = fb.shape[0]
+    rng = np.random.default_rng(5)
+    perm = torch.from_numpy(np.concatenate([[0], 1 + rng.permutation(n_b - 1)]).astype(np.int64))   # old id -> new id
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(n_b)
+    comps = (fa, fb[inv], wa, wb[inv], perm[a2b], b2a[inv], perm[b2revb[inv]], a_scope, b_scope, dop)
+    graph = _util.ComponentsGraph(comps)
+    model = _model(bmg, hidden=76, depth=4)
+    d_out = torch.randn(len(a_scope), 76, generator=torch.Generator().manual_seed(9))
+    out, grads = _util.run_fwd_bwd(model, graph, d_out)
+    assert not DeviceGraph.get(graph, DEV).rev_adjacent
+    weights = {k: v.detach().cpu() for k, v in model.encoder[0].state_dict().items() if k != "cached_zero_vector"}
+    ref_out, ref_grads = mpn_oracle.encoder_forward_backward(comps, weights, d_out, depth=4)
+    assert _golden.rel_err(out, ref_out) <= OUT_TOL
+    for k, ref in ref_grads.items():
+        assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
+    out0, _ = _util.run_fwd_bwd(model, bmg, d_out)
+    assert _golden.rel_err(out, out0) <= 1e-6                    # per-row arithmetic is the same, only row order moved
