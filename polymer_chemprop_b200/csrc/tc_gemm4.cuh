@@ -119,6 +119,14 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
       const int rr = rq + 4 * i;
       xv[i] = *reinterpret_cast<const float4*>(sl + rr * 128 + ((pc ^ (rr & 7)) << 4));
     }
+    // The slot is handed back BEFORE the global stores are issued: everything this warp needs is in registers now,
+    // and fence.proxy.async behaves like a MEMBAR that waits for the thread's outstanding global accesses -- placed
+    // after the stores (as it was) it serialised every 32-column chunk on the store latency (role wait-cycle
+    // counters, profiles/r1_k_t4_role_wait_breakdown.log: the epilogue was 77 % busy and the MMA waited 20 % of the
+    // kernel for a free accumulator).
+    ptx::fence_proxy_async_smem();            // generic accesses of the slot are ordered before the next TMA write
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
     float* cp = C + (row0 + we * 32 + rq) * ldc + colb;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -128,9 +136,6 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
       if (in_c && row0 + we * 32 + rq + 4 * i < M) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
     }
-    ptx::fence_proxy_async_smem();            // generic accesses of the slot are ordered before the next TMA write
-    __syncwarp();
-    if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
   }
 }
 
