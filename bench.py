@@ -334,7 +334,7 @@ def main():
     value = world * G / (ms_step * 1e-3)
 
     # ---- end to end: pinned host tensors -> H2D -> feature expansion + CSR build -> fwd+bwd -> D2H of the output
-    e2e, e2e_full = None, None
+    e2e, e2e_full, e2e_store = None, None, None
     if not a.no_e2e:
         comps = bmg.get_components()
         pinned = tuple(x.pin_memory() for x in comps[:7]) + tuple(comps[7:])
@@ -356,6 +356,8 @@ def main():
             rebuilt on the device instead of being uploaded; otherwise a foreign object that only offers
             get_components() (Python lists for the scopes, all seven tensors uploaded as they are)."""
             def next_batch():
+                if native == "store":                    # a freshly shuffled batch assembled in HBM from the resident store
+                    return store.batch(store_rng.permutation(len(graphs)), stream=copy_stream)
                 hg = bmg.fresh_view() if native else HostGraph(pinned)
                 DeviceGraph.prefetch(hg, dev, copy_stream)
                 return hg
@@ -396,6 +398,13 @@ def main():
                 dist.all_reduce(te, op=dist.ReduceOp.MAX)
             up = [bmg.f_atoms, bmg.f_bonds_tail, bmg.w_atoms, bmg.w_bonds, bmg.a2b, bmg.b2a, bmg.b2revb,
                   bmg.a_scope_array, bmg.dop_array] if native else list(pinned[:7])
+            if native == "store":
+                return {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
+                        "h2d_bytes_per_step": int(24 * G), "d2h_bytes_per_step": int(d2h), "steps": k,
+                        "ms_per_step_median": float(np.median(walls)), "store_bytes": int(store.nbytes),
+                        "api": "DeviceGraphStore.batch(shuffled indices, copy stream) || MPN.forward(batch) + backward + "
+                               "out -> pinned host; the featurised dataset is resident in HBM (uploaded once, outside the "
+                               "timed region), each step uploads only the selected indices and their offsets"}
             return {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
                     "h2d_bytes_per_step": int(nbytes(up) + (0 if native else G * 12)), "d2h_bytes_per_step": int(d2h),
                     "steps": k, "ms_per_step_median": float(np.median(walls)),
@@ -407,6 +416,12 @@ def main():
 
         e2e_full = run_e2e(False)
         e2e = run_e2e(True) if bmg.f_bonds_tail is not None else e2e_full
+        e2e_store = None
+        if bmg.f_bonds_tail is not None:
+            from polymer_chemprop_b200 import DeviceGraphStore
+            store = DeviceGraphStore(graphs, dev)        # BASELINE configs[4]: "dataset pre-staged on device"
+            store_rng = np.random.default_rng(rank)
+            e2e_store = run_e2e("store")
 
     if rank == 0:
         peak, peak_src = load_peaks()
@@ -442,7 +457,8 @@ def main():
                 "roofline": roof, "kernels": kernels,
                 "step_hbm": {"alg_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,
                              "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
-                "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "e2e_full_tensors": e2e_full}
+                "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "e2e_full_tensors": e2e_full,
+                "e2e_device_store": e2e_store}
         if not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(graphs, a)
         print(json.dumps(line), flush=True)

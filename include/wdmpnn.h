@@ -137,6 +137,40 @@ int wd_expand_features(const float* f_atoms, const float* bond_tail, const int64
                        int64_t n_bonds, int32_t atom_fdim, int32_t tail_fdim, float* f_atoms_out,
                        int32_t ld_atoms, float* f_bonds_out, int32_t ld_bonds, void* stream);
 
+/* A device-resident store of featurised graphs (the reference keeps them as host MolGraph objects cached in
+ * SMILES_TO_GRAPH, chemprop/data/data.py:30-40, :277-314) in compact, per-graph LOCAL numbering (atoms and bonds of
+ * a graph start at 0, as in MolGraph): all arrays are DEVICE pointers, graphs concatenated in store order. */
+typedef struct WdStore {
+  int64_t n_graphs;
+  int32_t atom_fdim;           /* F_a                                                          */
+  int32_t tail_fdim;           /* F_b - F_a: width of the bond-only part of a bond row          */
+  const float* f_atoms;        /* [sum n_atoms, F_a] dense                                      */
+  const float* bond_tail;      /* [sum n_bonds, F_b - F_a]: f_bonds[b] = [f_atoms[b2a[b]], bond_tail[b]] (featurization.py:467-468) */
+  const float* w_atoms;        /* [sum n_atoms]                                                 */
+  const float* w_bonds;        /* [sum n_bonds]                                                 */
+  const int32_t* b2a;          /* [sum n_bonds] local source atom                               */
+  const int32_t* b2revb;       /* [sum n_bonds] local reverse bond                              */
+  const int32_t* in_idx;       /* [sum n_bonds] local ids of incoming bonds, a2b rows concatenated in atom order */
+  const int32_t* out_idx;      /* [sum n_bonds] local ids of outgoing bonds (ascending), concatenated in atom order */
+  const int32_t* in_ptr_local; /* [sum n_atoms] exclusive prefix of the in-degrees within the graph */
+  const int64_t* atom_off;     /* [n_graphs + 1] first atom row of each graph in the store       */
+  const int64_t* bond_off;     /* [n_graphs + 1] first bond row of each graph in the store       */
+  const float* dop;            /* [n_graphs] degree_of_polym                                    */
+} WdStore;
+
+/* Assembles the batch made of graphs sel[0..n_mols) (DEVICE int64 store indices, repeats allowed) directly into the
+ * arrays of `out` -- what BatchMolGraph.__init__ (featurization.py:757-813) + wd_expand_features + wd_csr_build
+ * produce for the same graphs in the same order, bit for bit: row 0 padding, per-molecule offsets, padded feature
+ * rows (out->ld_atoms / ld_bonds), int32 CSR / reverse-CSR, src / rev / dst, mol_of, dop.
+ * a_start / a_size / b_start / b_size: DEVICE int32 [n_mols], the batch's scopes (a_scope / b_scope: starts are
+ * 1 + exclusive prefix sums of the sizes; the caller computes them on the host, where it also needs the totals to
+ * size the buffers); a_start / a_size are also what out->a_start / a_size point to.  bond_mol: DEVICE int32
+ * [out->n_bonds] scratch.  Every array of `out` is caller-allocated and OVERWRITTEN (the const in WdGraph's
+ * declarations is cast away). */
+int wd_store_assemble(const WdStore* store, const int64_t* sel, const int32_t* a_start, const int32_t* a_size,
+                      const int32_t* b_start, const int32_t* b_size, int64_t n_mols, const WdGraph* out,
+                      int32_t* bond_mol, void* stream);
+
 /* Bytes of caller-provided workspace.  The forward pass stores there what the backward pass
  * re-reads (I, M_t, A_t, H) plus scratch; pass the same buffer, untouched, to the backward. */
 size_t wd_workspace_bytes(const WdConfig* cfg, int64_t n_atoms, int64_t n_bonds, int64_t n_mols);

@@ -36,6 +36,12 @@ class WdGraph(C.Structure):
                 ("dop", C.c_void_p), ("ld_atoms", C.c_int32), ("ld_bonds", C.c_int32), ("rev_adjacent", C.c_int32)]
 
 
+class WdStore(C.Structure):
+    _fields_ = [("n_graphs", C.c_int64), ("atom_fdim", C.c_int32), ("tail_fdim", C.c_int32)] + \
+               [(n, C.c_void_p) for n in ("f_atoms", "bond_tail", "w_atoms", "w_bonds", "b2a", "b2revb", "in_idx", "out_idx",
+                                          "in_ptr_local", "atom_off", "bond_off", "dop")]
+
+
 class WdWeights(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("W_i", "b_i", "W_h", "b_h", "W_o", "b_o")]
 
@@ -44,7 +50,7 @@ class WdGrads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("dW_i", "db_i", "dW_h", "db_h", "dW_o", "db_o")]
 
 
-EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_workspace_bytes", "wd_encoder_forward",
+EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_store_assemble", "wd_workspace_bytes", "wd_encoder_forward",
            "wd_infer_workspace_bytes", "wd_encoder_infer",
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
@@ -74,6 +80,8 @@ def lib():
     L.wd_expand_features.argtypes = [vp, vp, vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, vp, C.c_int32, vp,
                                      C.c_int32, vp]
     L.wd_expand_features.restype = C.c_int
+    L.wd_store_assemble.argtypes = [C.POINTER(WdStore), vp, vp, vp, vp, vp, C.c_int64, C.POINTER(WdGraph), vp, vp]
+    L.wd_store_assemble.restype = C.c_int
     L.wd_csr_build_check.argtypes = [vp, vp]
     L.wd_csr_build_check.restype = C.c_int
     L.wd_workspace_bytes.argtypes = [C.POINTER(WdConfig), C.c_int64, C.c_int64, C.c_int64]

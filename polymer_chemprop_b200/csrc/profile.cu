@@ -69,5 +69,5 @@ extern "C" int wd_profile_read(int category, double* total_ms, int64_t* launches
   return WD_OK;
 }
 
-// ABI version of include/wdmpnn.h (3: wd_expand_features, wd_encoder_infer, WdConfig.dropout*)
+// ABI version of include/wdmpnn.h (3: wd_expand_features, wd_encoder_infer, wd_store_assemble, WdConfig.dropout*, WdGraph.rev_adjacent)
 extern "C" int wd_abi_version(void) { return 3; }

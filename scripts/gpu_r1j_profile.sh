@@ -3,16 +3,19 @@
 # the ncu launch list and one `ncu --set full` capture of the hot kernels of a bench step.
 set -u
 mkdir -p gpurun_out
-T=${WD_TAG:-r1_j}
+T=${WD_TAG:-r1_k}
 timeout 1200 python -m pytest tests -q -m gpu -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 timeout 300 python __graft_entry__.py smoke > gpurun_out/${T}_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/${T}_smoke.log
 timeout 900 python bench.py --steps 30 --warmup 5 > gpurun_out/${T}_bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -2 gpurun_out/bench.err
 timeout 300 python bench.py --steps 100 --warmup 10 --batch 50 --no-cpu-baseline > gpurun_out/${T}_bench_b50.json 2> gpurun_out/bench_b50.err; echo "bench b50 rc=$?"
 timeout 300 python bench.py --steps 50 --warmup 10 --batch 512 --no-cpu-baseline > gpurun_out/${T}_bench_b512.json 2> gpurun_out/bench_b512.err; echo "bench b512 rc=$?"
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
+timeout 300 python bench.py --steps 20 --warmup 5 --kind qm9 --no-cpu-baseline > gpurun_out/${T}_bench_qm9_b4096.json 2> gpurun_out/bench_qm9.err; echo "qm9 rc=$?"
+timeout 600 python bench.py --steps 5 --warmup 3 --hidden 2400 --depth 6 --batch 8192 --no-cpu-baseline --no-e2e > gpurun_out/${T}_bench_h2400_d6_b8192.json 2> gpurun_out/bench_h2400.err; echo "h2400 rc=$?"
+timeout 600 python bench.py --steps 5 --warmup 3 --math fp32 --no-cpu-baseline --no-e2e > gpurun_out/${T}_bench_fp32.json 2> gpurun_out/bench_fp32.err; echo "fp32 rc=$?"
 python - <<PY
 import json
-for f in ("${T}_bench", "${T}_bench_b512", "${T}_bench_b50"):
+for f in ("${T}_bench", "${T}_bench_b512", "${T}_bench_b50", "${T}_bench_qm9_b4096", "${T}_bench_h2400_d6_b8192", "${T}_bench_fp32"):
     try:
         d = json.load(open(f"gpurun_out/{f}.json"))
     except Exception as e:

@@ -216,3 +216,46 @@ def test_inference_path_equals_training_forward_bitwise():
         full = lib.wd_workspace_bytes(C.byref(cfg), bmg.n_atoms, bmg.n_bonds, len(bmg.a_scope))
         small = lib.wd_infer_workspace_bytes(C.byref(cfg), bmg.n_atoms, bmg.n_bonds, len(bmg.a_scope))
         assert 0 < small < 0.45 * full
+
+
+def _star_graph(rng, n_leaves):
+    """One hub atom bonded to n_leaves atoms (in-degree n_leaves: exercises long CSR lists and max_num_bonds >> 8)."""
+    n = n_leaves + 1
+    fa = synth._atom_features(rng, n, True)
+    fb = synth._bond_features(rng, n_leaves, True)
+    pairs = [(0, i) for i in range(1, n)]
+    w = [(float(rng.uniform(0.05, 1.0)), float(rng.uniform(0.05, 1.0))) for _ in pairs]
+    return synth._assemble(n, pairs, w, fa, fb, rng.uniform(0.2, 1.0, n).astype(np.float32), 1.0 + float(rng.uniform(1, 3)))
+
+
+@pytest.mark.parametrize("mode,out_tol,grad_tol", [("fp32", OUT_TOL, GRAD_TOL), ("tf32", 1e-3, 3e-2)])
+@pytest.mark.parametrize("case", ["depth1", "star_k40", "one_molecule_h8"])
+def test_edge_shapes_match_oracle(case, mode, out_tol, grad_tol):
+    """Edges of the shape space: depth 1 (no message passing, W_h unused: the reference leaves its grad None),
+    an atom with 40 incoming bonds (K = 40), a single molecule with hidden size 8."""
+    rng = np.random.default_rng(17)
+    if case == "depth1":
+        graphs, hidden, depth = synth.make_graphs("copolymer", 6, 81, dense_features=True, random_edge_weights=True), 44, 1
+    elif case == "star_k40":
+        graphs, hidden, depth = [_star_graph(rng, 40), synth.empty_graph(), _star_graph(rng, 3)], 76, 3
+    else:
+        graphs, hidden, depth = synth.make_graphs("qm9", 1, 82, dense_features=True), 8, 3
+    bmg = BatchMolGraph(graphs)
+    if case == "star_k40":
+        assert bmg.max_num_bonds == 40
+    torch.manual_seed(5)
+    model = _util.MPN(_util.make_args(hidden_size=hidden, depth=depth, wd_math_mode=mode), atom_fdim=bmg.atom_fdim,
+                      bond_fdim=bmg.bond_fdim).to(DEV)
+    for p in model.parameters():
+        if p.requires_grad:
+            torch.nn.init.normal_(p, 0.0, 0.1) if p.dim() == 1 else torch.nn.init.xavier_normal_(p)
+    d_out = torch.randn(len(bmg.a_scope), hidden, generator=torch.Generator().manual_seed(9))
+    out, grads = _util.run_fwd_bwd(model, bmg, d_out)
+    weights = {k: v.detach().cpu() for k, v in model.encoder[0].state_dict().items() if k != "cached_zero_vector"}
+    ref_out, ref_grads = mpn_oracle.encoder_forward_backward(bmg.get_components(), weights, d_out, depth=depth)
+    assert _golden.rel_err(out, ref_out) <= out_tol
+    for k, ref in ref_grads.items():
+        if ref is None:                                   # depth 1: W_h takes no part in the reference's graph
+            assert k not in grads
+            continue
+        assert _golden.rel_err(grads[k], ref) <= grad_tol, k
