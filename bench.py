@@ -144,17 +144,19 @@ def run_reference(a):
 # clocks during the timed region (B200_PROFILING.md "clocks line")
 # --------------------------------------------------------------------------------------------
 class ClockSampler:
+    """nvidia-smi polled every 20 ms from before the warm-up; only the lines that arrive between begin() and end()
+    -- the timed passes -- count (the process takes ~0.1 s to start, longer than a short timed region)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.proc, self.lines = index, None, []
+        self.index, self.proc, self.lines, self.t0, self.t1 = index, None, [], None, None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -162,17 +164,27 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def begin(self):
+        self.t0 = time.perf_counter()
+
+    def end(self):
+        self.t1 = time.perf_counter()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
         self.thread.join(timeout=2)
+        inside = [ln for t, ln in self.lines if self.t0 is not None and self.t0 <= t <= (self.t1 or t)]
+        window = "timed passes"
+        if not inside:                      # region shorter than one poll: the nearest samples taken under load
+            inside, window = [ln for _t, ln in self.lines[-5:]], "last samples before the end of the timed passes"
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
                 continue
@@ -185,7 +197,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 # --------------------------------------------------------------------------------------------
@@ -296,14 +308,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()                                  # polls from here on; only the timed passes are counted
     for _ in range(max(a.warmup, 3)):
         step()
     sync_all()
     lib = _capi.lib()
     lib.wd_profile_reset()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
 
     def timed(k):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -319,6 +331,7 @@ def main():
         return float(t.item()) / k
 
     # pass 1 -- the timed region of `value`: exactly K steps, nothing between the launches
+    sampler.begin()
     n0 = _capi.launch_count()
     ms_step = timed(a.steps)
     launches = _capi.launch_count() - n0
@@ -328,6 +341,7 @@ def main():
     lib.wd_profile_enable(1)
     ms_step_events = timed(a.steps)
     lib.wd_profile_enable(0)
+    sampler.end()
     clocks = sampler.stop() if rank == 0 else None
     prof = _capi.profile_read()
     lib.wd_profile_reset()
