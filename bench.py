@@ -203,20 +203,24 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------
 # algorithmic bytes per launch of each kernel category (DESIGN.md "Kernels and rooflines")
 # --------------------------------------------------------------------------------------------
-def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d):
+def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d, sign_bits=False):
     """Compulsory HBM bytes per launch of each kernel category (average over the launches of the category in one
-    step), for the algorithm as implemented: S_t is written by the forward depth steps and read back by dW_h."""
+    step), for the algorithm as implemented: S_t is written by the forward depth steps and read back by dW_h.
+    sign_bits: the forward epilogues leave one bit per element of I / M_t (TF32 mode, ReLU) and the message gradient
+    reads those (B words per launch) instead of the activation (P)."""
     P, Q = 4.0 * Nb * h, 4.0 * Na * h            # one [N_b,h] / [N_a,h] fp32 pass
+    B = 4.0 * Nb * ((h + 31) // 32) if sign_bits else 0.0
+    A = B if sign_bits else P                    # what the message gradient reads for act'
     steps = max(d - 1, 1)
-    depth_total = ((3 * P + Q) + (d - 2) * (4 * P + Q)) if d > 1 else 0.0    # t=1 reads I once; every step writes S_t
+    depth_total = ((3 * P + Q + B) + (d - 2) * (4 * P + Q + B)) if d > 1 else 0.0    # t=1 reads I once; every step writes S_t
     if d > 1:
-        msg_total = (2 * P + Q) + (d - 2) * (5 * P + Q) + (4 * P + Q)         # first / middle / last step
+        msg_total = (P + A + Q) + (d - 2) * (4 * P + A + Q) + (3 * P + A + Q)     # first / middle / last step
     else:
-        msg_total = 2 * P + Q
+        msg_total = P + A + Q
     dw_total = (2 * Q + 4.0 * Na * Fa) + (d - 1) * 2 * P + (P + 4.0 * Nb * Fb)   # dW_o, dW_h x (d-1), dW_i
     dx_total = 2 * Q + (d - 1) * 2 * P                                          # dA_d, dS x (d-1)
     return {
-        "input_proj": 4.0 * Nb * Fb + P + 4.0 * h * Fb,
+        "input_proj": 4.0 * Nb * Fb + P + B + 4.0 * h * Fb,
         "aggregate": P + Q + 12.0 * Nb + 4.0 * Na,
         "depth_step": depth_total / steps + 8.0 * Nb + 4.0 * h * h,
         "atom_update": 4.0 * Na * Fa + 2 * Q + 4.0 * h * (Fa + h),
@@ -348,7 +352,7 @@ def main():
     value = world * G / (ms_step * 1e-3)
 
     # ---- end to end: pinned host tensors -> H2D -> feature expansion + CSR build -> fwd+bwd -> D2H of the output
-    e2e, e2e_full, e2e_store = None, None, None
+    e2e, e2e_full, e2e_store, e2e_step_sync = None, None, None, None
     if not a.no_e2e:
         comps = bmg.get_components()
         pinned = tuple(x.pin_memory() for x in comps[:7]) + tuple(comps[7:])
@@ -361,14 +365,18 @@ def main():
         def nbytes(ts):
             return sum(x.numel() * x.element_size() for x in ts)
 
-        def run_e2e(native):
+        def run_e2e(native, sync="result"):
             """The public API with a one-batch look-ahead, as a data loader drives it: the upload + device-side
             graph build of batch i+1 run on a copy stream (DeviceGraph.prefetch) while the encoder step of
             batch i runs.  Every step uploads one full batch from pinned host memory and reads its encoder
             output back.  native: the batch is this package's BatchMolGraph (a fresh object per step, nothing
             cached on it), which carries f_bonds_tail and array forms of a_scope / degree_of_polym, so f_bonds is
             rebuilt on the device instead of being uploaded; otherwise a foreign object that only offers
-            get_components() (Python lists for the scopes, all seven tensors uploaded as they are)."""
+            get_components() (Python lists for the scopes, all seven tensors uploaded as they are).
+            sync: "result" -- the host blocks every step until that step's encoder output has arrived in pinned host
+            memory (what a training loop's loss.item() waits for) and then launches the next step while the backward
+            pass is still running; "step" -- the host also waits for the backward pass (and the gradient all-reduce)
+            before it launches anything of the next step, so the GPU idles during the host's launch prologue."""
             def next_batch():
                 if native == "store":                    # a freshly shuffled batch assembled in HBM from the resident store
                     return store.batch(store_rng.permutation(len(graphs)), stream=copy_stream)
@@ -380,6 +388,7 @@ def main():
 
             def e2e_step():
                 cur = state["next"]
+                state["next"] = next_batch()             # upload of batch i+1 overlaps the step of batch i
                 for p in params:
                     p.grad = None
                 out = model([cur])
@@ -392,9 +401,9 @@ def main():
                 out.backward(d_out)
                 if world > 1:
                     reducer()
-                state["next"] = next_batch()             # upload of batch i+1 overlaps the step of batch i
-                torch.cuda.current_stream().synchronize()
-                d2h_stream.synchronize()
+                if sync == "step":                       # host waits for the whole step (backward, all-reduce) as well
+                    torch.cuda.current_stream().synchronize()
+                d2h_stream.synchronize()                 # the step's result is on the host (what loss.item() waits for)
 
             for _ in range(3):
                 e2e_step()
@@ -415,13 +424,13 @@ def main():
             if native == "store":
                 return {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
                         "h2d_bytes_per_step": int(24 * G), "d2h_bytes_per_step": int(d2h), "steps": k,
-                        "ms_per_step_median": float(np.median(walls)), "store_bytes": int(store.nbytes),
+                        "ms_per_step_median": float(np.median(walls)), "store_bytes": int(store.nbytes), "host_sync": sync,
                         "api": "DeviceGraphStore.batch(shuffled indices, copy stream) || MPN.forward(batch) + backward + "
                                "out -> pinned host; the featurised dataset is resident in HBM (uploaded once, outside the "
                                "timed region), each step uploads only the selected indices and their offsets"}
             return {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
                     "h2d_bytes_per_step": int(nbytes(up) + (0 if native else G * 12)), "d2h_bytes_per_step": int(d2h),
-                    "steps": k, "ms_per_step_median": float(np.median(walls)),
+                    "steps": k, "ms_per_step_median": float(np.median(walls)), "host_sync": sync,
                     "api": "MPN.forward(batch) + backward + out -> pinned host || DeviceGraph.prefetch(next batch of "
                            "pinned CPU tensors, copy stream)",
                     "upload": ("f_atoms + bond-only tail of f_bonds (BatchMolGraph.f_bonds_tail) + weights + indices; "
@@ -430,6 +439,7 @@ def main():
 
         e2e_full = run_e2e(False)
         e2e = run_e2e(True) if bmg.f_bonds_tail is not None else e2e_full
+        e2e_step_sync = run_e2e(bmg.f_bonds_tail is not None, sync="step")
         e2e_store = None
         if bmg.f_bonds_tail is not None:
             from polymer_chemprop_b200 import DeviceGraphStore
@@ -439,7 +449,8 @@ def main():
 
     if rank == 0:
         peak, peak_src = load_peaks()
-        alg = algorithmic_bytes(Na, Nb, G, a.hidden, bmg.atom_fdim, bmg.bond_fdim, a.depth)
+        sign_bits = a.math == "tf32" and os.environ.get("WD_SIGN_BITS", "1") != "0"    # model activation is ReLU
+        alg = algorithmic_bytes(Na, Nb, G, a.hidden, bmg.atom_fdim, bmg.bond_fdim, a.depth, sign_bits)
         kernels = {}
         gpu_ms = sum(ms for ms, _n in prof.values())
         for name, (ms, n) in prof.items():
@@ -466,13 +477,13 @@ def main():
                 "config": {"workload": workload_name(a), "global_batch": world * G, "n_atoms": Na, "n_bonds": Nb,
                            "parallelism": f"dp{world}" if world > 1 else "single GPU",
                            "l2": "per-step working set (workspace >= 2 GB at batch 4096) exceeds the 126 MB L2",
-                           "math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0"},
+                           "math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0", "sign_bits": sign_bits},
                 "edge_msgs_per_s": world * (Nb - 1) * max(a.depth - 1, 0) / (ms_step * 1e-3),
                 "roofline": roof, "kernels": kernels,
                 "step_hbm": {"alg_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,
                              "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
                 "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "e2e_full_tensors": e2e_full,
-                "e2e_device_store": e2e_store}
+                "e2e_device_store": e2e_store, "e2e_host_waits_for_backward": e2e_step_sync}
         if not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(graphs, a)
         print(json.dumps(line), flush=True)

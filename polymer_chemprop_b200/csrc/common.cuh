@@ -163,6 +163,42 @@ __device__ __forceinline__ float4 act_bwd_dropped4(float4 y, const Dropout& d, i
                      act_bwd_from_out<ACT>(y.z * inv) * k.z, act_bwd_from_out<ACT>(y.w * inv) * k.w);
 }
 
+// Sign bits of a stored activation, written by the tensor-core epilogues and read by k_message_grad in place of
+// the activation itself when the derivative only needs (y > 0) (ReLU): 1 bit instead of 32 per element.
+// A "sign tile" is the column range one epilogue call covers (a column tile of the plain kernels, an accumulator
+// half of the gathered kernel; at most 160 columns = 5 words): column c belongs to column tile c / bn, half
+// (c % bn) / half of it.  Tile j stores its rows back to back: word (j * n_rows + row) * wpt + k covers the
+// tile's columns [32k, 32k + 32), and bit 8 * u + q of it is column 32k + 4q + u (q = 0..7, u = 0..3) -- the order
+// in which the epilogue's write-out lanes hold the columns (tc_gemm2.cuh: t2_epilogue), so a word is four ballots.
+struct SignBits {
+  uint32_t* p;                // nullptr: not written / not used
+  int64_t n_rows;
+  int bn, half, tpn, wpt;     // column tile width, sign tile width, sign tiles per column tile, words per sign tile row
+};
+__device__ __forceinline__ uint32_t sign_bits4(const SignBits& m, int64_t row, int c) {   // bits of columns c .. c+3 (c % 4 == 0)
+  const int nt = c / m.bn, cc = c - nt * m.bn, hb = cc / m.half, c2 = cc - hb * m.half;
+  const uint32_t w = __ldg(m.p + ((int64_t)(nt * m.tpn + hb) * m.n_rows + row) * m.wpt + (c2 >> 5));
+  return w >> ((c2 & 31) >> 2);          // bit 0 / 8 / 16 / 24 = column c / c+1 / c+2 / c+3
+}
+// Epilogue side: the 8 lanes (pc = lane & 7) of row group rq = lane >> 3 hold 32 columns of one row; lane pc keeps
+// the words of 32-column chunk pc for its 8 rows (sw[i]: row rq + 4 i) until the sign tile is complete.
+__device__ __forceinline__ void sign_collect(uint32_t& sw, float4 x, int rq, int pc, int chunk) {
+  const uint32_t b0 = __ballot_sync(0xffffffffu, x.x > 0.f), b1 = __ballot_sync(0xffffffffu, x.y > 0.f),
+                 b2 = __ballot_sync(0xffffffffu, x.z > 0.f), b3 = __ballot_sync(0xffffffffu, x.w > 0.f);
+  const int sh = 8 * rq;
+  const uint32_t w = ((b0 >> sh) & 0xffu) | (((b1 >> sh) & 0xffu) << 8) | (((b2 >> sh) & 0xffu) << 16) |
+                     (((b3 >> sh) & 0xffu) << 24);
+  if (pc == chunk) sw = w;
+}
+__device__ __forceinline__ void sign_flush(const SignBits& m, const uint32_t (&sw)[8], int tile, int64_t row_w0, int64_t M,
+                                           int rq, int pc, int n_chunks) {
+  if (pc >= n_chunks) return;
+  uint32_t* base = m.p + ((int64_t)tile * m.n_rows + row_w0 + rq) * m.wpt + pc;   // row_w0: first row of this warp
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+    if (row_w0 + rq + 4 * i < M) base[(int64_t)(4 * i) * m.wpt] = sw[i];
+}
+
 #define WD_DISPATCH_ACT(act, ...)                                          \
   switch (act) {                                                           \
     case WD_ACT_RELU: { constexpr int ACT = WD_ACT_RELU; __VA_ARGS__; } break;             \

@@ -23,6 +23,8 @@ struct Layout {
   int64_t szB, szA;        // floats per [N_b, ldh] / [N_a, ldh] buffer
   int64_t I, M, Agg, H, mscale, U, dZ, dZ2, dS, dI, dA, dZo, partials, total;
   int64_t S;               // TF32 mode: S_t = A_t[b2a] - M_{t-1}[b2revb] written by the forward depth steps, read by dW_h
+  int64_t Sign;            // TF32 mode + ReLU: sign bits of I and of every M_t (d x N_b x sign_ld words), see SignBits
+  int sign_ld;             // words per row (over all sign tiles); 0 = the backward pass reads the activations themselves
   int Z;                   // max row chunks of the weight-gradient contractions (sizes `partials`)
   int Zh, Zi, Zo;          // row chunks of the dW_h / dW_i / dW_o contractions
   TcPacked pWi, pWh, pWo, pWhT, pWoT;   // TF32 mode: packed weight images (img == offset holder until bound)
@@ -39,6 +41,12 @@ int dw_chunks(int64_t rows, int n1, int n2) {
   return (int)std::max<int64_t>(1, std::min<int64_t>(z, 64));
 }
 
+// sign-bit geometry of a producer tiled like `B`: a sign tile is a column tile of the plain kernels (<= 160 columns)
+// or an accumulator half of the gathered kernel (T4_HALF columns)
+int sign_words(const TcPacked& B) {
+  const int half = std::min(B.BN, T4_HALF);
+  return B.n_tiles * (int)ceil_div(B.BN, half) * (int)ceil_div(half, 32);
+}
 // infer: forward-only layout (wd_encoder_infer) -- two alternating message buffers, one aggregate buffer, nothing
 // kept for a backward pass (no S_t, no gradient scratch).
 Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool infer = false) {
@@ -81,6 +89,13 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
   L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
   L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h
   L.pWoT = tc_packed_geometry(h, h, 0);              // dA_d = dZo W_o[:, F_a:]
+  // the message gradient only needs (y > 0) of a ReLU output: the tensor-core epilogues leave those bits behind
+  const char* sign_env = getenv("WD_SIGN_BITS");      // read per call: tests and A/B runs flip it inside one process
+  const bool sign_off = sign_env && atoi(sign_env) == 0;
+  L.sign_ld = 0;
+  if (c.math_mode == WD_MATH_TF32 && !tc_use_v1() && !infer && c.activation == WD_ACT_RELU && !sign_off)
+    L.sign_ld = std::max(sign_words(L.pWi), sign_words(L.pWh));
+  L.Sign = take((int64_t)c.depth * Nb * L.sign_ld);
   const TcPacked* pk[5] = {&L.pWi, &L.pWh, &L.pWo, &L.pWhT, &L.pWoT};
   for (int i = 0; i < 5; ++i) L.pk[i] = take(c.math_mode == WD_MATH_TF32 && !(infer && i >= 3) ? pk[i]->floats() : 0);
   L.total = off;
@@ -131,14 +146,22 @@ Dropout make_dropout(const WdConfig& c, int salt) {
   return d;
 }
 
+// sign bits of activation `t` (0: input projection I, t >= 1: message M_t), produced by a kernel tiled like `B`
+SignBits sign_bits(const Layout& L, void* ws, int64_t Nb, int t, const TcPacked& B) {
+  if (L.sign_ld == 0) return SignBits{};
+  const int half = std::min(B.BN, T4_HALF);
+  return SignBits{reinterpret_cast<uint32_t*>(L.p(ws, L.Sign)) + (int64_t)t * Nb * L.sign_ld, Nb, B.BN, half,
+                  (int)ceil_div(B.BN, half), (int)ceil_div(half, 32)};
+}
+
 inline int grid1d(int64_t n, int block = 256) { return (int)ceil_div(std::max<int64_t>(n, 1), block); }
 
 // ---- contraction dispatch: FP32 -> SIMT FFMA kernels, TF32 -> tcgen05 kernels (tc == packed weights) ----
 template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
 int gemm(const WdConfig& c, cudaStream_t s, const AOperand& A, const float* W, int ldb, const float* bias,
          const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, const TcPacked* tc,
-         const Dropout& drop = Dropout{}) {
-  if (c.math_mode == WD_MATH_TF32) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M, drop);
+         const Dropout& drop = Dropout{}, const SignBits& sign = SignBits{}) {
+  if (c.math_mode == WD_MATH_TF32) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M, drop, sign);
   dim3 grid((unsigned)ceil_div(M, SG_BM), (unsigned)ceil_div(std::max(N, ldc), SG_BN));
   WD_LAUNCH((k_simt_gemm<AMODE, BMODE, EPI, ACT, PREACT>), grid, SG_THREADS, 0, s, A, W, ldb, bias, R, ldr,
             C, ldc, M, N, K, drop);
@@ -214,7 +237,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   AOperand a_in{g.f_bonds, nullptr, nullptr, nullptr, g.ld_bonds ? g.ld_bonds : Fb, 0, 0};
   { ProfScope ps(WD_PROF_INPUT_PROJ);
   WD_TRY((gemm<A_PLAIN, B_NK, E_STORE, ACT, false>(c, s, a_in, w.W_i, Fb, c.bias ? w.b_i : nullptr, nullptr, 0,
-                                                  I, ld, Nb, h, Fb, &L.pWi))); }
+                                                  I, ld, Nb, h, Fb, &L.pWi, Dropout{}, sign_bits(L, ws, Nb, 0, L.pWi)))); }
   const float* prev = I;   // message = act(input) is applied on load (PREACT)          :97
   for (int t = 1; t < c.depth; ++t) {                                               // :100
     const bool pre = (t == 1);
@@ -240,8 +263,9 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     if (c.math_mode == WD_MATH_TF32 && !tc_use_v1() && !infer) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
     const float* bh = c.bias ? w.b_h : nullptr;
     const Dropout drop = make_dropout(c, t);                                          // :124
-    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh, drop)));
-    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh, drop)));
+    const SignBits sg = sign_bits(L, ws, Nb, t, L.pWh);
+    if (upre) WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, true>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh, drop, sg)));
+    else      WD_TRY((gemm<A_GATHER_DIFF, B_NK, E_RES_ACT, ACT, false>(c, s, a_s, w.W_h, h, bh, I, ld, M_t, ld, Nb, h, h, &L.pWh, drop, sg)));
     prev = M_t;
   }
   // final aggregate + atom update                                                    :127-134
@@ -268,16 +292,27 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
 // ---- backward ---------------------------------------------------------------------------------
 template <int ACT, bool PREACT, bool HAS_DS, bool WRITE_DZ, bool WRITE_DI>
 int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const float* dA, const float* dS,
-                 const float* Y, int ld, float* dZ, const float* dI_in, float* dI, const Dropout& drop) {
+                 const float* Y, int ld, float* dZ, const float* dI_in, float* dI, const Dropout& drop,
+                 const SignBits& sb) {
   const int nc4 = ld / 4;
   const int64_t Nb = g.n_bonds;
   ProfScope ps(WD_PROF_MSG_GRAD);
+  constexpr bool kRelu = ACT == WD_ACT_RELU;   // the only activation whose derivative the sign bits carry
+  if (kRelu && sb.p != nullptr) {
+    if (c.undirected && HAS_DS)
+      WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, kRelu>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
+                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb);
+    else
+      WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, kRelu>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
+                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb);
+    return WD_OK;
+  }
   if (c.undirected && HAS_DS)
-    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
-              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop);
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, false>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
+              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{});
   else
-    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y, ld,
-              g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop);
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, false>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
+              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{});
   return WD_OK;
 }
 
@@ -335,8 +370,9 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     const float* M_prev = (t == 1) ? I : L.p(ws, L.M) + (int64_t)(t - 2) * L.szB;
     const bool pre = (t == 1);
     // dZ_t = dM_t * act'(M_t), dI += dZ_t ; dM_t = w_b dA[dst b] - dS[rev b] (symmetrised if undirected)
-    if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI, make_dropout(c, t)))); sum = dZ; }
-    else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI, make_dropout(c, t)))); sum = dI; }
+    const SignBits sg = sign_bits(L, ws, Nb, t, L.pWh);
+    if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI, make_dropout(c, t), sg))); sum = dZ; }
+    else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI, make_dropout(c, t), sg))); sum = dI; }
     // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
     const float* u = M_prev;
     bool upre = pre;
@@ -367,11 +403,11 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     { ProfScope ps(WD_PROF_DW);
     WD_TRY(reduce_partials(s, P, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
     if (c.bias && gr.db_h) WD_TRY(colsum(s, sum, ld, Pcol, gr.db_h, Nb, h, Zh)); }  // sum == sum_{t>=1} dZ_t here
-    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI, Dropout{})));
+    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI, Dropout{}, sign_bits(L, ws, Nb, 0, L.pWi))));
   } else {
     WD_CUDA_OK(cudaMemsetAsync(gr.dW_h, 0, sizeof(float) * h * h, s));
     if (c.bias && gr.db_h) WD_CUDA_OK(cudaMemsetAsync(gr.db_h, 0, sizeof(float) * h, s));
-    WD_TRY((message_grad<ACT, true, false, false, true>(c, s, g, dA, dS, I, ld, nullptr, nullptr, dI, Dropout{})));
+    WD_TRY((message_grad<ACT, true, false, false, true>(c, s, g, dA, dS, I, ld, nullptr, nullptr, dI, Dropout{}, sign_bits(L, ws, Nb, 0, L.pWi))));
   }
   {  // dW_i = dI^T f_bonds ; db_i = colsum(dI)
     ProfScope ps(WD_PROF_DW);

@@ -63,12 +63,14 @@ __global__ void k_symmetrize(const float* __restrict__ X, int ld, const int32_t*
 //   dZ[b] = g(b) * act'(Y[b])   with Y = M_t (PREACT: Y = act(I))
 //   dI[b] = (dI_in ? dI_in[b] : 0) + dZ[b]     (WRITE_DI; dI_in may alias dI or be the previous step's dZ)
 // WRITE_DZ = false for the last step (nothing reads dZ_0), WRITE_DI = false for the first one (dI == dZ then).
-template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool WRITE_DZ, bool WRITE_DI>
+// SIGNS (ReLU only): act'(Y) comes from the sign bits the forward epilogues left (common.cuh SignBits) instead of
+// from Y itself -- one 4-byte word per 32 columns is read in place of 128 bytes, and a dropped element has bit 0.
+template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool WRITE_DZ, bool WRITE_DI, bool SIGNS>
 __global__ void k_message_grad(const float* __restrict__ dA, const float* __restrict__ dS,
                                const float* __restrict__ Y, int ld, const float* __restrict__ w,
                                const int32_t* __restrict__ dst, const int32_t* __restrict__ rev,
                                float* __restrict__ dZ, const float* dI_in, float* dI, int64_t n_rows, int nc4,
-                               Dropout drop) {
+                               Dropout drop, SignBits sb) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_rows * nc4) return;
@@ -89,12 +91,20 @@ __global__ void k_message_grad(const float* __restrict__ dA, const float* __rest
       g.z = (g.z + (wr * dar.z - dsb.z)) / 2.f; g.w = (g.w + (wr * dar.w - dsb.w)) / 2.f;
     }
   }
-  float4 y = ldg4(Y + b * ld + c);
-  if (PREACT) y = f4_act<ACT>(y);
   float4 dy;                                   // d (stored activation) / d (pre-activation)
-  if (!PREACT && drop.thresh != 0u) dy = act_bwd_dropped4<ACT>(y, drop, b * ld + c);   // Y = dropout(act(z)), mpn.py:124
-  else dy = make_float4(act_bwd_from_out<ACT>(y.x), act_bwd_from_out<ACT>(y.y), act_bwd_from_out<ACT>(y.z),
-                        act_bwd_from_out<ACT>(y.w));
+  if (SIGNS) {
+    static_assert(!SIGNS || ACT == WD_ACT_RELU, "sign bits carry the derivative of ReLU only");
+    const uint32_t bits = sign_bits4(sb, b, c);
+    const float on = (!PREACT && drop.thresh != 0u) ? drop.scale : 1.f;     // kept elements were scaled by 1 / (1 - p)
+    dy = make_float4((bits & 1u) ? on : 0.f, (bits & 0x100u) ? on : 0.f, (bits & 0x10000u) ? on : 0.f,
+                     (bits & 0x1000000u) ? on : 0.f);
+  } else {
+    float4 y = ldg4(Y + b * ld + c);
+    if (PREACT) y = f4_act<ACT>(y);
+    if (!PREACT && drop.thresh != 0u) dy = act_bwd_dropped4<ACT>(y, drop, b * ld + c);   // Y = dropout(act(z)), mpn.py:124
+    else dy = make_float4(act_bwd_from_out<ACT>(y.x), act_bwd_from_out<ACT>(y.y), act_bwd_from_out<ACT>(y.z),
+                          act_bwd_from_out<ACT>(y.w));
+  }
   float4 dz = make_float4(g.x * dy.x, g.y * dy.y, g.z * dy.z, g.w * dy.w);
   if (WRITE_DZ) st4(dZ + b * ld + c, dz);
   if (WRITE_DI) {

@@ -80,7 +80,8 @@ template <int EPI, int ACT>
 __device__ __forceinline__ void t2_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T2Barriers* bar,
                                             uint32_t& rit, int BN, int64_t row0, int64_t M, int col0, int N, int cmax,
                                             const float* bias, float* C, int ldc, long long* tacc,
-                                            const Dropout& drop) {
+                                            const Dropout& drop, const SignBits& sign) {
+  uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
   for (int c0 = 0; c0 < BN; c0 += 32, ++rit) {
     const int slot = rit % T2_R_SLOTS;
     uint8_t* sl = rring + slot * T2_R_SLOT_BYTES + (we * 32) * T2_R_ROW;     // this warp's 32 rows
@@ -130,10 +131,12 @@ __device__ __forceinline__ void t2_epilogue(uint32_t tmem_acc, int we, int lane,
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
       const bool ok = in_c && row0 + we * 32 + rq + 4 * i < M && !(WD_ABL & 4);
       if (ok) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
+      if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
     }
     __syncwarp();
     if (EPI == E_RES_ACT && lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
   }
+  if (sign.p != nullptr) sign_flush(sign, sw, col0 / BN, row0 + we * 32, M, lane >> 3, lane & 7, (BN + 31) >> 5);
 }
 
 // One K segment of the virtual A operand.
@@ -160,6 +163,7 @@ struct T2Params {
   float* S;             // optional copy of the virtual A operand (segment 0, before rounding), [M, lds]
   int lds;
   Dropout drop;         // applied after the activation (EPI != E_STORE)
+  SignBits sign;        // (stored value > 0) bits, written next to C when sign.p != nullptr
 };
 
 template <int NSRC, int EPI, int ACT, bool PREACT>
@@ -417,7 +421,7 @@ __global__ void __launch_bounds__(T2_THREADS, 1) k_tc_gemm2(const T2Params p) {
       T2_WAIT(7, &bar->tmem_full[acc], (tl / nacc) & 1);
       ptx::tc_fence_after();
       t2_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, bar, rit, p.BN, row0, p.M, col0, p.N, p.ldc,
-                            p.bias, p.C, p.ldc, tacc, p.drop);
+                            p.bias, p.C, p.ldc, tacc, p.drop, p.sign);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);

@@ -36,6 +36,7 @@ struct T3Params {
   int64_t M;
   int N, BN, n_tiles;
   Dropout drop;         // applied after the activation (EPI == E_ACT)
+  SignBits sign;        // (stored value > 0) bits, written next to C when sign.p != nullptr
 };
 
 inline int t3_smem_bytes(int BN) {
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
       T2_WAIT(7, &bar->tmem_full[acc], (tl >> 1) & 1);
       ptx::tc_fence_after();
       t2_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, ebar, rit, p.BN, row0, p.M, col0, p.N, p.ldc,
-                            p.bias, p.C, p.ldc, tacc, p.drop);
+                            p.bias, p.C, p.ldc, tacc, p.drop, p.sign);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);

@@ -64,6 +64,7 @@ struct T4Params {
   float* S;             // optional copy of the operand rows, [M, lds]
   int lds;
   Dropout drop;         // applied after the activation
+  SignBits sign;        // (stored value > 0) bits, written next to C when sign.p != nullptr
   CUtensorMap mx1;      // X1[M, K] (FLOAT32, box 132 rows x 32 columns, SWIZZLE_128B), used when x1_tma != 0
   int x1_tma;           // 1: i1(r) == ((r-1)^1)+1 for every r >= 1 (adjacent reverse pairs): X1 rows arrive by TMA
 };
@@ -79,7 +80,8 @@ template <int ACT>
 __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T4Barriers* bar,
                                             uint32_t& rit, int W, int64_t row0, int64_t M, int col0, int N, int cmax,
                                             const float* bias, float* C, int ldc, long long* tacc,
-                                            const Dropout& drop) {
+                                            const Dropout& drop, const SignBits& sign, int sign_tile) {
+  uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
   for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
     const int slot = rit % T4_R_SLOTS;
     uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
@@ -135,8 +137,10 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
       if (drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
       if (in_c && row0 + we * 32 + rq + 4 * i < M) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
+      if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
     }
   }
+  if (sign.p != nullptr) sign_flush(sign, sw, sign_tile, row0 + we * 32, M, lane >> 3, lane & 7, (W + 31) >> 5);
 }
 
 template <int ACT, bool PREACT>
@@ -365,7 +369,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         T2_WAIT(7, &bar->tmem_full[buf], (g / 3) & 1);
         ptx::tc_fence_after();
         t4_epilogue<ACT>(tmem_base + buf * T4_HALF, warp, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
-                         col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop);
+                         col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop, p.sign,
+                         (int)(tile % p.n_tiles) * p.sign.tpn + hb);
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[buf]);

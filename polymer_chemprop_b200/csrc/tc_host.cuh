@@ -78,9 +78,10 @@ inline int tc_set_smem(Kernel k, int bytes) {
 // second-generation kernel (cp.async raw ring + transform warps)
 template <int AMODE, int EPI, int ACT, bool PREACT>
 int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
-             float* C, int ldc, int64_t M, const Dropout& drop) {
+             float* C, int ldc, int64_t M, const Dropout& drop, const SignBits& sign) {
   T2Params p{};
   p.drop = drop;
+  p.sign = sign;
   constexpr int NSRC = AMODE == A_GATHER_DIFF ? 2 : 1;
   if (AMODE == A_GATHER_DIFF) {
     p.seg[0] = T2Seg{A.X, A.X2, A.src, A.rev, A.ldx, A.ldx2, B.K1, 1};
@@ -110,9 +111,10 @@ int tc_gemm2(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
 // fourth-generation kernel for the gathered depth step (column tiles up to 304 wide, in-place transform, TMA residual)
 template <int ACT, bool PREACT>
 int tc_gemm4(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
-             float* C, int ldc, int64_t M, const Dropout& drop) {
+             float* C, int ldc, int64_t M, const Dropout& drop, const SignBits& sign) {
   T4Params p{};
   p.drop = drop;
+  p.sign = sign;
   if (!tc_aligned16(A.X, A.ldx) || !tc_aligned16(A.X2, A.ldx2) || !tc_aligned16(R, ldr) || !tc_aligned16(C, ldc))
     return fail(WD_ERR_INVALID_ARG, "tcgen05 gathered step needs 16-byte aligned rows");
   if (B.BN > T4_MAX_BN || B.K2 != 0) return fail(WD_ERR_UNSUPPORTED, "tcgen05 gathered step: unsupported tile geometry");
@@ -147,9 +149,10 @@ inline bool tc_use_gemm3() {   // WD_TC_GEMM=2 keeps plain operands on the secon
 // third-generation kernel for plain / concatenated A operands: TMA tensor copies, no transform pass
 template <int AMODE, int EPI, int ACT>
 int tc_gemm3(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, float* C, int ldc, int64_t M,
-             const Dropout& drop) {
+             const Dropout& drop, const SignBits& sign) {
   T3Params p{};
   p.drop = drop;
+  p.sign = sign;
   int rc = tma_make_2d(&p.ma[0], A.X, M, B.K1, A.ldx, TC_BM, TMA_SW128);
   if (rc != WD_OK) return rc;
   if (AMODE == A_CONCAT) {
@@ -173,40 +176,41 @@ int tc_gemm3(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
 template <int AMODE, int EPI, int ACT, bool PREACT>
 struct TcGemm3Dispatch {   // the TMA kernel exists for plain operands and the store / activation epilogues only
   static int run(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, float* C, int ldc, int64_t M,
-                 const Dropout& drop) {
-    return tc_gemm3<AMODE, EPI, ACT>(s, A, B, bias, C, ldc, M, drop);
+                 const Dropout& drop, const SignBits& sign) {
+    return tc_gemm3<AMODE, EPI, ACT>(s, A, B, bias, C, ldc, M, drop, sign);
   }
   static constexpr bool ok = true;
 };
 template <int EPI, int ACT, bool PREACT>
 struct TcGemm3Dispatch<A_GATHER_DIFF, EPI, ACT, PREACT> {
-  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t, const Dropout&) { return WD_ERR_UNSUPPORTED; }
+  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t, const Dropout&, const SignBits&) { return WD_ERR_UNSUPPORTED; }
   static constexpr bool ok = false;
 };
 template <int AMODE, int ACT, bool PREACT>
 struct TcGemm3Dispatch<AMODE, E_RES_ACT, ACT, PREACT> {
-  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t, const Dropout&) { return WD_ERR_UNSUPPORTED; }
+  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t, const Dropout&, const SignBits&) { return WD_ERR_UNSUPPORTED; }
   static constexpr bool ok = false;
 };
 template <int ACT, bool PREACT>
 struct TcGemm3Dispatch<A_GATHER_DIFF, E_RES_ACT, ACT, PREACT> {
-  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t, const Dropout&) { return WD_ERR_UNSUPPORTED; }
+  static int run(cudaStream_t, const AOperand&, const TcPacked&, const float*, float*, int, int64_t, const Dropout&, const SignBits&) { return WD_ERR_UNSUPPORTED; }
   static constexpr bool ok = false;
 };
 
 // C[M, ldc] = epi( A[M, K1+K2] * B^T ) with B packed
 template <int AMODE, int EPI, int ACT, bool PREACT>
 int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
-            float* C, int ldc, int64_t M, const Dropout& drop = Dropout{}) {
+            float* C, int ldc, int64_t M, const Dropout& drop = Dropout{}, const SignBits& sign = SignBits{}) {
   if (!tc_use_v1()) {
-    if (AMODE == A_GATHER_DIFF && EPI == E_RES_ACT && B.BN > T2_MAX_BN) return tc_gemm4<ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M, drop);
+    if (AMODE == A_GATHER_DIFF && EPI == E_RES_ACT && B.BN > T2_MAX_BN) return tc_gemm4<ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M, drop, sign);
     using D3 = TcGemm3Dispatch<AMODE, EPI, ACT, PREACT>;
     if (D3::ok && tc_use_gemm3() && B.BN <= T2_MAX_BN && tc_aligned16(A.X, A.ldx) && tc_aligned16(C, ldc) &&
         (AMODE != A_CONCAT || tc_aligned16(A.X2, A.ldx2)))
-      return D3::run(s, A, B, bias, C, ldc, M, drop);
-    return tc_gemm2<AMODE, EPI, ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M, drop);
+      return D3::run(s, A, B, bias, C, ldc, M, drop, sign);
+    return tc_gemm2<AMODE, EPI, ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M, drop, sign);
   }
   if (drop.thresh != 0u) return fail(WD_ERR_UNSUPPORTED, "WD_TC_V1 kernels do not implement dropout");
+  if (sign.p != nullptr) return fail(WD_ERR_UNSUPPORTED, "WD_TC_V1 kernels do not write sign bits");
   TcGemmParams p{};
   p.A = A;
   p.A.K1 = B.K1;

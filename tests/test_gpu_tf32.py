@@ -206,3 +206,26 @@ def test_renumbered_bonds_take_the_gathered_path_and_match_the_oracle():
         assert _golden.rel_err(grads[k], ref) <= GRAD_TOL, k
     out0, _ = _util.run_fwd_bwd(model, bmg, d_out)
     assert _golden.rel_err(out, out0) <= 1e-6                    # per-row arithmetic is the same, only row order moved
+
+
+@pytest.mark.parametrize("hidden,depth,undirected,p", [(300, 4, False, 0.0), (300, 3, True, 0.0), (76, 4, False, 0.0),
+                                                       (640, 2, False, 0.0), (300, 3, False, 0.25), (96, 3, False, 0.4)])
+def test_sign_bits_give_the_same_gradients_as_the_stored_activations_bitwise(hidden, depth, undirected, p, monkeypatch):
+    """ReLU: the message gradient reads one sign bit per element (left by the tcgen05 epilogues, common.cuh
+    SignBits) instead of the stored activation.  Same arithmetic (act' is 0 or 1, times the dropout scale), so
+    every gradient must agree bit for bit with the path that reads the activations (WD_SIGN_BITS=0).  The widths
+    cover one and two column tiles per producer and both depth-step kernels (k_tc_gemm4 / k_tc_gemm2)."""
+    bmg = _big_batch()
+    model = _model(bmg, hidden=hidden, depth=depth, undirected=undirected, dropout=p)
+    model.train()
+    d_out = torch.randn(len(bmg.a_scope), hidden, generator=torch.Generator().manual_seed(2))
+    enc = model.encoder[0]
+    res = {}
+    for bits in ("1", "0"):
+        monkeypatch.setenv("WD_SIGN_BITS", bits)
+        torch.manual_seed(77)                                    # same dropout seed for both runs
+        res[bits] = _util.run_fwd_bwd(model, bmg, d_out)
+    assert torch.equal(res["1"][0], res["0"][0])
+    assert len(res["1"][1]) >= 3
+    for k in res["1"][1]:
+        assert torch.equal(res["1"][1][k], res["0"][1][k]), k
