@@ -176,7 +176,9 @@ struct SignBits {
   int bn, half, tpn, wpt;     // column tile width, sign tile width, sign tiles per column tile, words per sign tile row
 };
 __device__ __forceinline__ uint32_t sign_bits4(const SignBits& m, int64_t row, int c) {   // bits of columns c .. c+3 (c % 4 == 0)
-  const int nt = c / m.bn, cc = c - nt * m.bn, hb = cc / m.half, c2 = cc - hb * m.half;
+  int nt = 0, cc = c;                    // column tile / half by subtraction: one or two steps, cheaper than dividing
+  while (cc >= m.bn) { cc -= m.bn; ++nt; }
+  const int hb = cc >= m.half ? 1 : 0, c2 = cc - hb * m.half;      // at most two halves per column tile
   const uint32_t w = __ldg(m.p + ((int64_t)(nt * m.tpn + hb) * m.n_rows + row) * m.wpt + (c2 >> 5));
   return w >> ((c2 & 31) >> 2);          // bit 0 / 8 / 16 / 24 = column c / c+1 / c+2 / c+3
 }

@@ -298,21 +298,23 @@ int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const floa
   const int64_t Nb = g.n_bonds;
   ProfScope ps(WD_PROF_MSG_GRAD);
   constexpr bool kRelu = ACT == WD_ACT_RELU;   // the only activation whose derivative the sign bits carry
+  // rows per block: up to MG_ROWS, but at least ~16 blocks per SM so that small batches still fill the machine
+  const int rpb = (int)std::max<int64_t>(4, std::min<int64_t>(MG_ROWS, Nb / (16 * kNumSMs)));
   if (kRelu && sb.p != nullptr) {
     if (c.undirected && HAS_DS)
-      WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, kRelu>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
-                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb);
+      WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, kRelu>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
+                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb, rpb);
     else
-      WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, kRelu>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
-                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb);
+      WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, kRelu>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
+                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb, rpb);
     return WD_OK;
   }
   if (c.undirected && HAS_DS)
-    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, false>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
-              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{});
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, false>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
+              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{}, rpb);
   else
-    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, false>), grid1d(Nb * nc4), 256, 0, s, dA, dS, Y,
-              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{});
+    WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, false>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
+              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{}, rpb);
   return WD_OK;
 }
 

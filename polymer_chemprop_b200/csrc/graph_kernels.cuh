@@ -63,6 +63,8 @@ __global__ void k_symmetrize(const float* __restrict__ X, int ld, const int32_t*
 //   dZ[b] = g(b) * act'(Y[b])   with Y = M_t (PREACT: Y = act(I))
 //   dI[b] = (dI_in ? dI_in[b] : 0) + dZ[b]     (WRITE_DI; dI_in may alias dI or be the previous step's dZ)
 // WRITE_DZ = false for the last step (nothing reads dZ_0), WRITE_DI = false for the first one (dI == dZ then).
+constexpr int MG_ROWS = 64;   // most rows per block of k_message_grad (fewer when the batch is small: see message_grad())
+
 // SIGNS (ReLU only): act'(Y) comes from the sign bits the forward epilogues left (common.cuh SignBits) instead of
 // from Y itself -- one 4-byte word per 32 columns is read in place of 128 bytes, and a dropped element has bit 0.
 template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool WRITE_DZ, bool WRITE_DI, bool SIGNS>
@@ -70,12 +72,19 @@ __global__ void k_message_grad(const float* __restrict__ dA, const float* __rest
                                const float* __restrict__ Y, int ld, const float* __restrict__ w,
                                const int32_t* __restrict__ dst, const int32_t* __restrict__ rev,
                                float* __restrict__ dZ, const float* dI_in, float* dI, int64_t n_rows, int nc4,
-                               Dropout drop, SignBits sb) {
+                               Dropout drop, SignBits sb, int rows_per_block) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_rows * nc4) return;
-  int64_t b = i / nc4;
-  int c = (int)(i - b * nc4) * 4;
+  // A block walks rows_per_block (<= MG_ROWS) consecutive rows as one flat run of (row, column quad) elements, 256 at a time: adjacent
+  // lanes touch adjacent 16-byte words exactly as a flat grid would, but the element -> (row, column) split is a
+  // float multiply on a block-local index instead of a 64-bit division.  ncu had this kernel ISSUE-bound (issue
+  // slots 78 % busy at 3.1 TB/s for the first step): with the sign bits it moves as little as 20 bytes per element.
+  const int64_t row_base = (int64_t)blockIdx.x * rows_per_block;
+  const int n_el = (int)min((int64_t)rows_per_block, n_rows - row_base) * nc4;
+  const float inv = 1.f / (float)nc4;
+  for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
+  const int rl = (int)(((float)e + 0.5f) * inv);          // exact: e < MG_ROWS * nc4 < 2^22, (e + 0.5) / nc4 is >= 0.5 / nc4 away from an integer
+  const int64_t b = row_base + rl;
+  const int c = (e - rl * nc4) * 4;
   float wb = __ldg(w + b);
   float4 da = ldg4(dA + (int64_t)__ldg(dst + b) * ld + c);
   float4 g = make_float4(wb * da.x, wb * da.y, wb * da.z, wb * da.w);
@@ -113,6 +122,7 @@ __global__ void k_message_grad(const float* __restrict__ dA, const float* __rest
       dz = make_float4(di.x + dz.x, di.y + dz.y, di.z + dz.z, di.w + dz.w);
     }
     st4(dI + b * ld + c, dz);
+  }
   }
 }
 
