@@ -154,6 +154,12 @@ SignBits sign_bits(const Layout& L, void* ws, int64_t Nb, int t, const TcPacked&
                   (int)ceil_div(B.BN, half), (int)ceil_div(half, 32)};
 }
 
+// rows per block of the kernels that walk block-local runs of rows (k_message_grad, k_aggregate, k_readout_grad):
+// up to MG_ROWS, but at least ~16 blocks per SM so that small batches still fill the machine
+inline int rows_per_block(int64_t n_rows) {
+  return (int)std::max<int64_t>(4, std::min<int64_t>(MG_ROWS, n_rows / (16 * kNumSMs)));
+}
+
 inline int grid1d(int64_t n, int block = 256) { return (int)ceil_div(std::max<int64_t>(n, 1), block); }
 
 // ---- contraction dispatch: FP32 -> SIMT FFMA kernels, TF32 -> tcgen05 kernels (tc == packed weights) ----
@@ -211,8 +217,9 @@ int aggregate(cudaStream_t s, const WdGraph& g, bool incoming, const float* U, i
   const int64_t Na = g.n_atoms;
   // (a padded [N_a, K] int32 form of the lists -- one 16-byte id load at a fixed address instead of the ptr -> idx
   //  chain -- was measured 5 % SLOWER on B200, profiles/r1_j_padded_lists_vs_csr.txt, and removed)
-  WD_LAUNCH((k_aggregate<ACT, PREACT>), grid1d(Na * nc4), 256, 0, s, U, ld, w, g.in_ptr,
-            incoming ? g.in_idx : g.out_idx, out, Na, nc4);
+  const int rpb = rows_per_block(Na);
+  WD_LAUNCH((k_aggregate<ACT, PREACT>), (unsigned)ceil_div(Na, rpb), 256, 0, s, U, ld, w, g.in_ptr,
+            incoming ? g.in_idx : g.out_idx, out, Na, nc4, rpb);
   return WD_OK;
 }
 
@@ -298,8 +305,7 @@ int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const floa
   const int64_t Nb = g.n_bonds;
   ProfScope ps(WD_PROF_MSG_GRAD);
   constexpr bool kRelu = ACT == WD_ACT_RELU;   // the only activation whose derivative the sign bits carry
-  // rows per block: up to MG_ROWS, but at least ~16 blocks per SM so that small batches still fill the machine
-  const int rpb = (int)std::max<int64_t>(4, std::min<int64_t>(MG_ROWS, Nb / (16 * kNumSMs)));
+  const int rpb = rows_per_block(Nb);
   if (kRelu && sb.p != nullptr) {
     if (c.undirected && HAS_DS)
       WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, kRelu>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
@@ -341,12 +347,13 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
 
   // readout + atom-update activation:  dZo = w_a * dop/den * d_out[mol] * act'(H)
   { ProfScope ps(WD_PROF_READOUT);
+  const int rpb = rows_per_block(Na);
   if (h % 4 == 0 && (reinterpret_cast<uintptr_t>(d_out) & 15) == 0)
-    WD_LAUNCH((k_readout_grad<ACT, true>), grid1d(Na * nc4), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
-              L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth));
+    WD_LAUNCH((k_readout_grad<ACT, true>), (unsigned)ceil_div(Na, rpb), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
+              L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth), rpb);
   else
-    WD_LAUNCH((k_readout_grad<ACT, false>), grid1d(Na * nc4), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
-              L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth)); }
+    WD_LAUNCH((k_readout_grad<ACT, false>), (unsigned)ceil_div(Na, rpb), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
+              L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth), rpb); }
   {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zo;

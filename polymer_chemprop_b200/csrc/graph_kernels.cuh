@@ -13,12 +13,16 @@ namespace wd {
 template <int ACT, bool PREACT>
 __global__ void k_aggregate(const float* __restrict__ U, int ld, const float* __restrict__ w,
                             const int32_t* __restrict__ ptr, const int32_t* __restrict__ idx,
-                            float* __restrict__ out, int64_t n_rows, int nc4) {
+                            float* __restrict__ out, int64_t n_rows, int nc4, int rows_per_block) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_rows * nc4) return;
-  int64_t a = i / nc4;
-  int c = (int)(i - a * nc4) * 4;
+  // block-local run of rows, element index split by a float multiply (see k_message_grad)
+  const int64_t row_base = (int64_t)blockIdx.x * rows_per_block;
+  const int n_el = (int)min((int64_t)rows_per_block, n_rows - row_base) * nc4;
+  const float inv = 1.f / (float)nc4;
+  for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
+  const int rl = (int)(((float)e + 0.5f) * inv);
+  const int64_t a = row_base + rl;
+  const int c = (e - rl * nc4) * 4;
   int j0 = __ldg(ptr + a), j1 = __ldg(ptr + a + 1);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   // four rows in flight per thread (lists hold ~3 entries): indices first, then the independent row loads;
@@ -41,6 +45,7 @@ __global__ void k_aggregate(const float* __restrict__ U, int ld, const float* __
     }
   }
   st4(out + a * ld + c, acc);
+  }
 }
 
 // U[b] = (X(b) + X(rev b)) / 2      (mpn.py:101-102)
@@ -168,13 +173,17 @@ template <int ACT, bool VEC4>
 __global__ void k_readout_grad(const float* __restrict__ d_out, int h, const float* __restrict__ H,
                                int ld, const float* __restrict__ w_atoms,
                                const int32_t* __restrict__ mol_of, const float* __restrict__ mscale,
-                               float* __restrict__ dZo, int64_t n_atoms, Dropout drop) {
+                               float* __restrict__ dZo, int64_t n_atoms, Dropout drop, int rows_per_block) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   const int nc4 = ld / 4;
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_atoms * nc4) return;
-  int64_t a = i / nc4;
-  int c = (int)(i - a * nc4) * 4;
+  // block-local run of rows, element index split by a float multiply (see k_message_grad)
+  const int64_t row_base = (int64_t)blockIdx.x * rows_per_block;
+  const int n_el = (int)min((int64_t)rows_per_block, n_atoms - row_base) * nc4;
+  const float inv = 1.f / (float)nc4;
+  for (int e = threadIdx.x; e < n_el; e += blockDim.x) {
+  const int rl = (int)(((float)e + 0.5f) * inv);
+  const int64_t a = row_base + rl;
+  const int c = (e - rl * nc4) * 4;
   int g = __ldg(mol_of + a);
   float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
   if (g >= 0 && c < h) {
@@ -200,6 +209,7 @@ __global__ void k_readout_grad(const float* __restrict__ d_out, int h, const flo
     v.w = c + 3 < h ? s * d.w * dy.w : 0.f;
   }
   st4(dZo + a * ld + c, v);
+  }
 }
 
 }  // namespace wd
