@@ -220,6 +220,31 @@ enum {
   WD_PROF_REDUCE = 10,     /* fixed-order reduction of split-K partials, bias-gradient column sums */
   WD_PROF_NUM = 11
 };
+/* ---- fused optimiser step ---------------------------------------------------------------
+ * The reference updates the model with torch.optim.Adam / AdamW over model.parameters() (chemprop/utils.py:295-310,
+ * build_optimizer: one parameter group, lr = init_lr, weight_decay), after an optional nn.utils.clip_grad_norm_
+ * (chemprop/train/train.py:80-82); the learning rate is set per step by NoamLR (chemprop/nn_utils.py:115-194).
+ * Here the parameters live in ONE flat fp32 buffer (the gradients already do: the data-parallel all-reduce packs them)
+ * and one call does clip + Adam for all of them.  Same arithmetic as torch's single-tensor Adam (not amsgrad, not
+ * maximize):
+ *   scale = max_grad_norm > 0 ? min(1, max_grad_norm / (||grads||_2 + 1e-6)) : 1        (clip_grad_norm_)
+ *   g = scale * grad;  decoupled == 0: g += weight_decay * p   |   decoupled != 0: p *= 1 - lr * weight_decay
+ *   m += (1 - beta1) * (g - m);  v = beta2 * v + (1 - beta2) * g * g
+ *   p -= (lr / (1 - beta1^step)) * m / (sqrt(v) / sqrt(1 - beta2^step) + eps)
+ * The squared norm is reduced in a fixed order (deterministic).  grad_norm_out (DEVICE float, may be NULL) receives
+ * ||grads||_2 when max_grad_norm > 0. */
+typedef struct WdAdam {
+  double lr, beta1, beta2, eps, weight_decay;   /* doubles, as torch holds them: 1 - beta, lr / (1 - beta1^step) and
+                                                   1 / sqrt(1 - beta2^step) are formed in double, then rounded to fp32 */
+  double max_grad_norm;        /* <= 0: no clipping                                                            */
+  int64_t step;                /* 1-based count of this update                                                 */
+  int32_t decoupled;           /* 0: Adam (L2 added to the gradient), 1: AdamW (decoupled decay)              */
+} WdAdam;
+/* scratch: DEVICE floats, >= wd_adam_scratch_floats() (norm partials); may be NULL when max_grad_norm <= 0. */
+int64_t wd_adam_scratch_floats(void);
+int wd_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const WdAdam* cfg,
+                 float* scratch, float* grad_norm_out, void* stream);
+
 void wd_profile_enable(int on); /* on != 0: record events around every launch from now on      */
 void wd_profile_reset(void);    /* forget recorded launches (keeps the event pool)              */
 /* Synchronises the recorded events and returns total milliseconds and launch count of category. */

@@ -2,3 +2,4 @@
 from .graph import BatchMolGraph, MolGraphData, ATOM_FDIM, BOND_FDIM  # noqa: F401
 from .mpn import MPN, MPNEncoder, DeviceGraph, install  # noqa: F401,E402
 from .store import DeviceGraphStore, StoreBatch  # noqa: F401,E402
+from .optim import FlatAdam, NoamLR  # noqa: F401,E402

@@ -36,6 +36,11 @@ class WdGraph(C.Structure):
                 ("dop", C.c_void_p), ("ld_atoms", C.c_int32), ("ld_bonds", C.c_int32), ("rev_adjacent", C.c_int32)]
 
 
+class WdAdam(C.Structure):
+    _fields_ = [("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
+                ("weight_decay", C.c_double), ("max_grad_norm", C.c_double), ("step", C.c_int64), ("decoupled", C.c_int32)]
+
+
 class WdStore(C.Structure):
     _fields_ = [("n_graphs", C.c_int64), ("atom_fdim", C.c_int32), ("tail_fdim", C.c_int32)] + \
                [(n, C.c_void_p) for n in ("f_atoms", "bond_tail", "w_atoms", "w_bonds", "b2a", "b2revb", "in_idx", "out_idx",
@@ -54,11 +59,11 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_store
            "wd_infer_workspace_bytes", "wd_encoder_infer",
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
-           "wd_debug_dw", "wd_debug_timing")
+           "wd_debug_dw", "wd_debug_timing", "wd_adam_scratch_floats", "wd_adam_step")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
-ABI_VERSION = 3      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features
+ABI_VERSION = 4      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step
 _lib = None
 
 
@@ -82,6 +87,10 @@ def lib():
     L.wd_expand_features.restype = C.c_int
     L.wd_store_assemble.argtypes = [C.POINTER(WdStore), vp, vp, vp, vp, vp, C.c_int64, C.POINTER(WdGraph), vp, vp]
     L.wd_store_assemble.restype = C.c_int
+    L.wd_adam_scratch_floats.argtypes = []
+    L.wd_adam_scratch_floats.restype = C.c_int64
+    L.wd_adam_step.argtypes = [vp, vp, vp, vp, C.c_int64, C.POINTER(WdAdam), vp, vp, vp]
+    L.wd_adam_step.restype = C.c_int
     L.wd_csr_build_check.argtypes = [vp, vp]
     L.wd_csr_build_check.restype = C.c_int
     L.wd_workspace_bytes.argtypes = [C.POINTER(WdConfig), C.c_int64, C.c_int64, C.c_int64]

@@ -116,3 +116,27 @@ def test_install_makes_the_reference_model_build_this_encoder():
             model([BatchMolGraph(synth.make_graphs("qm9", 2, 0))])
     finally:
         cm.MPN, cmpn.MPN, cmpn.MPNEncoder = saved
+
+
+def test_noam_lr_oracle_and_mirror_equal_live_reference_scheduler():
+    """chemprop/nn_utils.py:115-194 driven as chemprop/train/train.py:82-86 drives it, next to the product's mirror
+    and the oracle formula: equal learning rates to the last bit at every step, including the step the base class
+    takes inside the constructor."""
+    import importlib
+    from oracle import optim_oracle
+    from polymer_chemprop_b200 import NoamLR
+    ref_shim.load_reference()
+    RefNoam = importlib.import_module("chemprop.nn_utils").NoamLR
+    def cfg():   # fresh lists per scheduler: the reference keeps (and then overwrites) the caller's init_lr list (:157, :188)
+        return dict(warmup_epochs=[1.5], total_epochs=[5], steps_per_epoch=11, init_lr=[2e-4], max_lr=[3e-3], final_lr=[5e-5])
+    opts = [torch.optim.Adam([torch.nn.Parameter(torch.zeros(2))], lr=2e-4) for _ in range(2)]
+    a, b = RefNoam(optimizer=opts[0], **cfg()), NoamLR(opts[1], **cfg())
+    for _ in range(60):
+        assert a.current_step == b.current_step
+        assert opts[0].param_groups[0]["lr"] == opts[1].param_groups[0]["lr"] == a.get_lr()[0] == b.get_lr()[0]
+        assert optim_oracle.noam_lr(a.current_step, 1.5, 5, 11, 2e-4, 3e-3, 5e-5) == opts[0].param_groups[0]["lr"]
+        for o in opts:
+            o.param_groups[0]["params"][0].grad = torch.ones(2)
+            o.step()
+        a.step()
+        b.step()
