@@ -8,6 +8,7 @@ A step = MPN.forward(batch) + out.backward(d_out) on one batch (+ one NCCL all-r
 flat gradient when N > 1).  Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement".
 """
 import argparse
+import ctypes as C
 import json
 import os
 import subprocess
@@ -447,6 +448,29 @@ def main():
             store_rng = np.random.default_rng(rank)
             e2e_store = run_e2e("store")
 
+    # ---- forward-only inference path (predict / fingerprint; wd_encoder_infer) ----------------
+    inference = None
+    if rank == 0:
+        with torch.no_grad():
+            for _ in range(3):
+                model([bmg])
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            n1 = _capi.launch_count()
+            e0.record()
+            for _ in range(a.steps):
+                model([bmg])
+            e1.record()
+            torch.cuda.synchronize()
+        ms_inf = e0.elapsed_time(e1) / a.steps
+        cfg_inf = model.encoder[0].last_config
+        inference = {"value": G / (ms_inf * 1e-3), "unit": UNIT, "ms_per_step": ms_inf,
+                     "gpu_launches_per_step": (_capi.launch_count() - n1) / a.steps,
+                     "workspace_bytes": int(_capi.lib().wd_infer_workspace_bytes(C.byref(cfg_inf), Na, Nb, G)),
+                     "training_workspace_bytes": int(_capi.lib().wd_workspace_bytes(C.byref(cfg_inf), Na, Nb, G)),
+                     "note": "MPN.forward under torch.no_grad() on the resident batch of one GPU: forward kernels only, "
+                             "two alternating message buffers, nothing kept for a backward pass"}
+
     # ---- optimiser step over the encoder's parameters (not part of `value` / `e2e`) ----------
     optimizer_step = None
     if rank == 0 and not a.no_e2e:
@@ -512,7 +536,7 @@ def main():
                              "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
                 "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "e2e_full_tensors": e2e_full,
                 "e2e_device_store": e2e_store, "e2e_host_waits_for_backward": e2e_step_sync,
-                "optimizer_step": optimizer_step}
+                "optimizer_step": optimizer_step, "inference": inference}
         if not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(graphs, a)
         print(json.dumps(line), flush=True)
