@@ -354,18 +354,22 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   else
     WD_LAUNCH((k_readout_grad<ACT, false>), (unsigned)ceil_div(Na, rpb), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
               L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth), rpb); }
-  {  // dW_o = dZo^T [f_atoms, A_d] ; db_o = colsum(dZo)
+  // dZo (114 MB at B=4096) has just been written and fits L2: its three readers run back to back, smallest first
+  {  // db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
-    const int Z = L.Zo;
-    AOperand y{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
-    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, P, Na, h, Z)));
-    WD_TRY(reduce_partials(s, P, gr.dW_o, (int64_t)h * Fo, Z));
-    WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, Z));
+    WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, L.Zo));
   }
   // dA_d = dZo * W_o[:, F_a:]
   AOperand a_zo{dZo, nullptr, nullptr, nullptr, ld, 0, 0};
   { ProfScope ps(WD_PROF_DX);
   WD_TRY((gemm<A_PLAIN, B_KN, E_STORE, ACT, false>(c, s, a_zo, w.W_o + Fa, Fo, nullptr, nullptr, 0, dA, ld, Na, h, h, &L.pWoT))); }
+  {  // dW_o = dZo^T [f_atoms, A_d]
+    ProfScope ps(WD_PROF_DW);
+    const int Z = L.Zo;
+    AOperand y{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
+    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, P, Na, h, Z)));
+    WD_TRY(reduce_partials(s, P, gr.dW_o, (int64_t)h * Fo, Z));
+  }
 
   const int Zh = L.Zh;
   // dZ_t alternates between two buffers so that step t-1 can read dZ_t (as the running sum) while it writes its own;

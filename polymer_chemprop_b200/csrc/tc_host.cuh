@@ -1,5 +1,8 @@
 // Host-side launch helpers of the tcgen05 contraction kernels (tc_gemm.cuh / tc_dw.cuh).
 #pragma once
+#include <map>
+#include <mutex>
+#include <utility>
 #include "tc_gemm3.cuh"
 #include "tc_gemm4.cuh"
 #include "tc_dw.cuh"
@@ -69,9 +72,20 @@ inline int tc_pack(cudaStream_t s, const float* W, int ldb, int bmode, const TcP
 
 inline bool tc_aligned16(const void* p, int ld) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (ld & 3) == 0; }
 
+// The dynamic shared memory limit of a kernel is a sticky per-device attribute: set it once per (kernel, device, size)
+// instead of on every launch (one driver call per tensor-core launch on the host's critical path at small batches).
 template <typename Kernel>
 inline int tc_set_smem(Kernel k, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, int> done;    // (kernel, device) -> bytes already granted
+  int dev = 0;
+  WD_CUDA_OK(cudaGetDevice(&dev));
+  const std::pair<const void*, int> key(reinterpret_cast<const void*>(k), dev);
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = done.find(key);
+  if (it != done.end() && it->second == bytes) return WD_OK;
   WD_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done[key] = bytes;
   return WD_OK;
 }
 
