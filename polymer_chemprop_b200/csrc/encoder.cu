@@ -22,6 +22,7 @@ struct Layout {
   int ldh;                 // row stride of every [*, h] activation buffer (h rounded up to 4)
   int64_t szB, szA;        // floats per [N_b, ldh] / [N_a, ldh] buffer
   int64_t I, M, Agg, H, mscale, U, dZ, dZ2, dS, dI, dA, dZo, partials, total;
+  int64_t Po, Ph, Pi, Pcol;   // split-K partials of dW_o / dW_h (all steps) / dW_i, column-sum partials of db_o, db_h, db_i
   int64_t S;               // TF32 mode: S_t = A_t[b2a] - M_{t-1}[b2revb] written by the forward depth steps, read by dW_h
   int64_t Sign;            // TF32 mode + ReLU: sign bits of I and of every M_t (d x N_b x sign_ld words), see SignBits
   int sign_ld;             // words per row (over all sign tiles); 0 = the backward pass reads the activations themselves
@@ -81,9 +82,12 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
     L.Zo = dw_chunks(Na, h, Fo);
   }
   L.Z = std::max(std::max(L.Zh, L.Zi), L.Zo);
-  int64_t pw = std::max<int64_t>((int64_t)std::max(1, c.depth - 1) * h * h,
-                                 (int64_t)h * std::max(Fo, c.bond_fdim));
-  L.partials = take(infer ? 0 : (int64_t)L.Z * pw + (int64_t)kColsumMaxChunks * h);
+  // every reduction of the backward pass keeps its own partials until the single reduce launch at its end
+  L.Po = take(infer ? 0 : (int64_t)L.Zo * h * Fo);
+  L.Ph = take(infer ? 0 : (int64_t)std::max(0, c.depth - 1) * L.Zh * h * h);
+  L.Pi = take(infer ? 0 : (int64_t)L.Zi * h * c.bond_fdim);
+  L.Pcol = take(infer ? 0 : (int64_t)3 * kColsumMaxChunks * h);
+  L.partials = L.Po;
   L.pWi = tc_packed_geometry(h, c.bond_fdim, 0);     // I = f_bonds W_i^T
   L.pWh = tc_packed_geometry(h, h, 0, tc_use_gemm4() ? T4_MAX_BN : T2_MAX_BN);   // S W_h^T (gathered depth step)
   L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
@@ -193,19 +197,42 @@ int bind_packed(const WdConfig& c, Layout& L, void* ws) {
   return WD_OK;
 }
 
+// Reductions of one pass, collected and issued as ONE launch (ReduceJobs); every job keeps its own partial buffer
+// until then.  The order of the additions inside a job is fixed, so the result does not depend on the batching.
+struct Reducer {
+  ReduceJobs jobs{};
+  unsigned blocks = 0;
+  int add(const float* P, float* out, int64_t n, int Z) {
+    if (jobs.count >= RP_MAX_JOBS) return fail(WD_ERR_UNSUPPORTED, "too many reductions in one pass");
+    jobs.j[jobs.count++] = ReduceJob{P, out, n, Z, blocks};
+    blocks += (unsigned)ceil_div(n, RP_COLS);
+    return WD_OK;
+  }
+  int run(cudaStream_t s) {
+    if (jobs.count == 0) return WD_OK;
+    ProfScope ps(WD_PROF_REDUCE);
+    WD_LAUNCH(k_reduce_partials, blocks, RP_COLS * RP_GROUPS, 0, s, jobs);
+    jobs.count = 0;
+    blocks = 0;
+    return WD_OK;
+  }
+};
+
 int reduce_partials(cudaStream_t s, const float* P, float* out, int64_t n, int Z) {
-  ProfScope ps(WD_PROF_REDUCE);
-  WD_LAUNCH(k_reduce_partials, (unsigned)ceil_div(n, RP_COLS), RP_COLS * RP_GROUPS, 0, s, P, out, n, Z);
-  return WD_OK;
+  Reducer r;
+  r.add(P, out, n, Z);
+  return r.run(s);
 }
 
-// bias gradients: column sums over many short row chunks (coalesced row reads), then a fixed-order reduction
-int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_t R, int N, int /*Zdw*/) {
-  ProfScope ps(WD_PROF_REDUCE);
-  const int Z = (int)std::max<int64_t>(1, std::min<int64_t>(kColsumMaxChunks, R / 64));
+// bias gradients: column sums over many short row chunks (coalesced row reads) into P; the fixed-order reduction of
+// the chunks is queued on `red`
+int colsum_chunks(int64_t R) { return (int)std::max<int64_t>(1, std::min<int64_t>(kColsumMaxChunks, R / 64)); }
+int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_t R, int N, Reducer& red) {
+  const int Z = colsum_chunks(R);
   int64_t rpc = ceil_div(R, Z);
-  WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc);
-  return reduce_partials(s, P, out, N, Z);
+  { ProfScope ps(WD_PROF_REDUCE);
+  WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc); }
+  return red.add(P, out, N, Z);
 }
 
 #define WD_TRY(expr) do { int _rc = (expr); if (_rc != WD_OK) return _rc; } while (0)
@@ -340,9 +367,10 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   const int64_t Na = g.n_atoms, Nb = g.n_bonds;
   const int d = c.depth;
   float *I = L.p(ws, L.I), *H = L.p(ws, L.H), *dS = L.p(ws, L.dS), *dI = L.p(ws, L.dI),
-        *dA = L.p(ws, L.dA), *dZo = L.p(ws, L.dZo), *P = L.p(ws, L.partials);
-  const int64_t pw = std::max<int64_t>((int64_t)std::max(1, d - 1) * h * h, (int64_t)h * std::max(Fo, Fb));
-  float* Pcol = P + (int64_t)L.Z * pw;   // column-sum partials
+        *dA = L.p(ws, L.dA), *dZo = L.p(ws, L.dZo);
+  float *Po = L.p(ws, L.Po), *Ph = L.p(ws, L.Ph), *Pi = L.p(ws, L.Pi), *Pcol = L.p(ws, L.Pcol);
+  const int64_t pcol = (int64_t)kColsumMaxChunks * h;    // one column-sum region per bias gradient
+  Reducer red;                                            // all reductions of this pass: one launch at the end
   float* A_d = L.p(ws, L.Agg) + (int64_t)(d - 1) * L.szA;
 
   // readout + atom-update activation:  dZo = w_a * dop/den * d_out[mol] * act'(H)
@@ -357,7 +385,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   // dZo (114 MB at B=4096) has just been written and fits L2: its three readers run back to back, smallest first
   {  // db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
-    WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, L.Zo));
+    WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, red));
   }
   // dA_d = dZo * W_o[:, F_a:]
   AOperand a_zo{dZo, nullptr, nullptr, nullptr, ld, 0, 0};
@@ -367,8 +395,8 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zo;
     AOperand y{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
-    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, P, Na, h, Z)));
-    WD_TRY(reduce_partials(s, P, gr.dW_o, (int64_t)h * Fo, Z));
+    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, Po, Na, h, Z)));
+    WD_TRY(red.add(Po, gr.dW_o, (int64_t)h * Fo, Z));
   }
 
   const int Zh = L.Zh;
@@ -398,7 +426,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
       upre = false;
     }
     AOperand y{A_t, u, g.src, g.rev, ld, ld, 0};
-    float* Pt = P + (int64_t)(d - 1 - t) * Zh * h * h;
+    float* Pt = Ph + (int64_t)(d - 1 - t) * Zh * h * h;
     { ProfScope ps(WD_PROF_DW);
     if (have_S) {   // the forward pass left S_t in the workspace: a plain TMA-fed contraction
       AOperand ys{L.p(ws, L.S) + (int64_t)(t - 1) * L.szB, nullptr, nullptr, nullptr, ld, 0, 0};
@@ -414,8 +442,8 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   }
   if (d > 1) {
     { ProfScope ps(WD_PROF_DW);
-    WD_TRY(reduce_partials(s, P, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
-    if (c.bias && gr.db_h) WD_TRY(colsum(s, sum, ld, Pcol, gr.db_h, Nb, h, Zh)); }  // sum == sum_{t>=1} dZ_t here
+    WD_TRY(red.add(Ph, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
+    if (c.bias && gr.db_h) WD_TRY(colsum(s, sum, ld, Pcol + pcol, gr.db_h, Nb, h, red)); }  // sum == sum_{t>=1} dZ_t here
     WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI, Dropout{}, sign_bits(L, ws, Nb, 0, L.pWi))));
   } else {
     WD_CUDA_OK(cudaMemsetAsync(gr.dW_h, 0, sizeof(float) * h * h, s));
@@ -426,11 +454,11 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zi;
     AOperand y{g.f_bonds, nullptr, nullptr, nullptr, g.ld_bonds ? g.ld_bonds : Fb, 0, 0};
-    WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s, dI, ld, y, Fb, 0, P, Nb, h, Z)));
-    WD_TRY(reduce_partials(s, P, gr.dW_i, (int64_t)h * Fb, Z));
-    if (c.bias && gr.db_i) WD_TRY(colsum(s, dI, ld, Pcol, gr.db_i, Nb, h, Z));
+    WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s, dI, ld, y, Fb, 0, Pi, Nb, h, Z)));
+    WD_TRY(red.add(Pi, gr.dW_i, (int64_t)h * Fb, Z));
+    if (c.bias && gr.db_i) WD_TRY(colsum(s, dI, ld, Pcol + 2 * pcol, gr.db_i, Nb, h, red));
   }
-  return WD_OK;
+  return red.run(s);
 }
 
 }  // namespace

@@ -196,13 +196,34 @@ __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __
 // (ascending z inside a range, four independent accumulators), then the range sums are added in ascending order:
 // a fixed association order, hence bitwise reproducible; the split keeps 8x more loads in flight than one
 // thread walking all Z partials (Z is ~74..148 at batch 4096).
-constexpr int RP_COLS = 32, RP_GROUPS = 8;
-__global__ void __launch_bounds__(RP_COLS * RP_GROUPS)
-k_reduce_partials(const float* __restrict__ P, float* __restrict__ out, int64_t n, int Z) {
+constexpr int RP_COLS = 32, RP_GROUPS = 8, RP_MAX_JOBS = 8;
+// One launch reduces several partial buffers (a backward pass has up to six: dW_o, db_o, dW_h, db_h, dW_i, db_i):
+// every reduction is tiny, so separate launches were latency-bound -- 5 x 22 us at batch 4096, a fifth of the step
+// at batch 50.  Job j owns blocks [block0, block0 + ceil(n / RP_COLS)).
+struct ReduceJob {
+  const float* P;
+  float* out;
+  int64_t n;
+  int Z;
+  unsigned block0;
+};
+struct ReduceJobs {
+  ReduceJob j[RP_MAX_JOBS];
+  int count;
+};
+__global__ void __launch_bounds__(RP_COLS * RP_GROUPS) k_reduce_partials(const ReduceJobs jobs) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   __shared__ float part[RP_GROUPS][RP_COLS];
+  int ji = 0;
+#pragma unroll
+  for (int k = 1; k < RP_MAX_JOBS; ++k)
+    if (k < jobs.count && blockIdx.x >= jobs.j[k].block0) ji = k;
+  const float* __restrict__ P = jobs.j[ji].P;
+  float* __restrict__ out = jobs.j[ji].out;
+  const int64_t n = jobs.j[ji].n;
+  const int Z = jobs.j[ji].Z;
   const int tx = threadIdx.x & (RP_COLS - 1), ty = threadIdx.x / RP_COLS;
-  const int64_t i = (int64_t)blockIdx.x * RP_COLS + tx;
+  const int64_t i = (int64_t)(blockIdx.x - jobs.j[ji].block0) * RP_COLS + tx;
   const int z0 = (int)((int64_t)Z * ty / RP_GROUPS), z1 = (int)((int64_t)Z * (ty + 1) / RP_GROUPS);
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   if (i < n) {
