@@ -34,9 +34,19 @@ enum { WD_ACT_RELU = 0, WD_ACT_LEAKY_RELU = 1, WD_ACT_TANH = 2, WD_ACT_SELU = 3,
 /* aggregation: chemprop/models/mpn.py:158-163 */
 enum { WD_AGG_MEAN = 0, WD_AGG_SUM = 1, WD_AGG_NORM = 2 };
 /* math_mode: arithmetic of the h x h / F x h contractions.
- *   FP32  : CUDA-core FFMA, fp32 accumulate              (parity <= 1e-5 relative)
- *   TF32  : tcgen05.mma kind::tf32, fp32 accumulate in TMEM (parity <= 1e-3 relative) */
-enum { WD_MATH_FP32 = 0, WD_MATH_TF32 = 1 };
+ *   FP32   : CUDA-core FFMA, fp32 accumulate                 (encoder output <= 1e-5 relative; the slow parity path)
+ *   TF32   : tcgen05.mma kind::tf32, one pass, fp32 accumulate in TMEM
+ *                                                            (encoder output <= 1e-3, predictions ~5e-4)
+ *   TF32X3 : tcgen05.mma kind::tf32 with error compensation in the FORWARD contractions: both operands are split
+ *            into tf32 hi + lo parts and a_hi w_hi + a_lo w_hi + a_hi w_lo accumulate in the same TMEM tile
+ *            (fp32-grade forward: encoder output <= 1e-5, predictions <= 1e-4, the north-star bound); the backward
+ *            contractions stay single-pass TF32.  The default of the Python drop-in. */
+enum { WD_MATH_FP32 = 0, WD_MATH_TF32 = 1, WD_MATH_TF32X3 = 2 };
+/* WdConfig.flags */
+#define WD_FLAG_NO_SIGN_BITS 1u /* tensor-core modes, ReLU: the backward reads the stored activations instead of the  */
+                                /* 1-bit-per-element sign images the forward epilogues leave (A/B and test switch).   */
+                                /* Part of the config, so the forward and the backward call of a step always agree.   */
+#define WD_FLAG_NO_GRAPH 2u     /* never replay the call's launches through a CUDA graph (see wd_encoder_forward)     */
 
 /* Encoder configuration == the TrainArgs fields MPNEncoder.__init__ reads (mpn.py:24-35). */
 typedef struct WdConfig {
@@ -54,6 +64,7 @@ typedef struct WdConfig {
   uint32_t dropout_seed_lo; /* Philox key of this call's masks; pass the SAME cfg to the backward call.        */
   uint32_t dropout_seed_hi; /* The reference's RNG stream cannot be matched: masks are Philox4x32-10 words of  */
                             /* (element index, site) -- restated in oracle/mpn_oracle.py for the parity tests.  */
+  uint32_t flags;           /* WD_FLAG_* bits; 0 = defaults                                                     */
 } WdConfig;
 
 /* One BatchMolGraph on the device: get_components() tensors (featurization.py:815-846) plus the
@@ -251,7 +262,7 @@ void wd_profile_reset(void);    /* forget recorded launches (keeps the event poo
 int wd_profile_read(int category, double* total_ms, int64_t* launches);
 
 /* Test hooks: the raw contractions behind the encoder on plain row-major operands, so that the
- * tensor-core kernels can be checked in isolation (tests/test_gpu_contractions.py).
+ * tensor-core kernels can be checked in isolation (tests/test_gpu_tf32.py).
  * wd_debug_gemm: C[M, ldc] = epi(A[M,K] * B^T + bias (+ R)); B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k];
  *   epi 0 = store, 1 = ReLU, 2 = ReLU(R + .).  Columns [N, ldc) of C are zero-filled.
  *   TF32 mode needs `scratch` >= 4 * round_up(N,304-ish tiles) * round_up(K,32) bytes (packed weights).

@@ -14,7 +14,8 @@ LIB_PATH = os.environ.get("WDMPNN_LIB") or os.path.join(_HERE, "libwdmpnn.so")
 WD_OK, WD_ERR_INVALID_ARG, WD_ERR_CUDA, WD_ERR_UNSUPPORTED, WD_ERR_GRAPH = 0, -1, -2, -3, -4
 ACTIVATIONS = {"ReLU": 0, "LeakyReLU": 1, "tanh": 2, "SELU": 3, "ELU": 4}
 AGGREGATIONS = {"mean": 0, "sum": 1, "norm": 2}
-MATH_MODES = {"fp32": 0, "tf32": 1}
+MATH_MODES = {"fp32": 0, "tf32": 1, "tf32x3": 2}
+FLAG_NO_SIGN_BITS, FLAG_NO_GRAPH = 1, 2
 
 _f32p, _i32p, _i64p = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int64)
 
@@ -24,7 +25,7 @@ class WdConfig(C.Structure):
                 ("depth", C.c_int32), ("activation", C.c_int32), ("aggregation", C.c_int32),
                 ("undirected", C.c_int32), ("bias", C.c_int32), ("math_mode", C.c_int32),
                 ("aggregation_norm", C.c_float), ("dropout", C.c_float), ("dropout_seed_lo", C.c_uint32),
-                ("dropout_seed_hi", C.c_uint32)]
+                ("dropout_seed_hi", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class WdGraph(C.Structure):
@@ -63,7 +64,8 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_store
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
-ABI_VERSION = 4      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step
+ABI_VERSION = 5      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step,
+                     # 5 = WdConfig.flags, WD_MATH_TF32X3
 _lib = None
 
 

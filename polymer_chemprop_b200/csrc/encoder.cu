@@ -26,6 +26,7 @@ struct Layout {
   int64_t S;               // TF32 mode: S_t = A_t[b2a] - M_{t-1}[b2revb] written by the forward depth steps, read by dW_h
   int64_t Sign;            // TF32 mode + ReLU: sign bits of I and of every M_t (d x N_b x sign_ld words), see SignBits
   int sign_ld;             // words per row (over all sign tiles); 0 = the backward pass reads the activations themselves
+  bool tc;                 // tensor-core math mode (TF32 or TF32X3)
   int Z;                   // max row chunks of the weight-gradient contractions (sizes `partials`)
   int Zh, Zi, Zo;          // row chunks of the dW_h / dW_i / dW_o contractions
   TcPacked pWi, pWh, pWo, pWhT, pWoT;   // TF32 mode: packed weight images (img == offset holder until bound)
@@ -50,9 +51,13 @@ int sign_words(const TcPacked& B) {
 }
 // infer: forward-only layout (wd_encoder_infer) -- two alternating message buffers, one aggregate buffer, nothing
 // kept for a backward pass (no S_t, no gradient scratch).
+inline bool is_tc(const WdConfig& c) { return c.math_mode == WD_MATH_TF32 || c.math_mode == WD_MATH_TF32X3; }
+
 Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool infer = false) {
   Layout L;
   const int h = c.hidden_size;
+  const bool tc = is_tc(c), x3 = c.math_mode == WD_MATH_TF32X3;
+  L.tc = tc;
   L.ldh = (int)round_up(h, 8);   // rows start on 32-byte sectors: a 128-byte row chunk is exactly 4 sectors
   L.szB = round_up(Nb * L.ldh, 64);
   L.szA = round_up(Na * L.ldh, 64);
@@ -64,7 +69,7 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
   L.H = take(L.szA);
   L.mscale = take(G);
   L.U = take(c.undirected ? L.szB : 0);
-  L.S = take(c.math_mode == WD_MATH_TF32 && !infer ? (int64_t)std::max(0, c.depth - 1) * L.szB : 0);
+  L.S = take(tc && !infer ? (int64_t)std::max(0, c.depth - 1) * L.szB : 0);
   L.dZ = take(infer ? 0 : L.szB);
   L.dZ2 = take(c.depth > 2 && !infer ? L.szB : 0);
   L.dS = take(infer ? 0 : L.szB);
@@ -72,7 +77,7 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
   L.dA = take(infer ? 0 : L.szA);
   L.dZo = take(infer ? 0 : L.szA);
   const int Fo = c.atom_fdim + h;
-  if (c.math_mode == WD_MATH_TF32) {
+  if (tc) {
     L.Zh = tc_dw_z(Nb, h, tc_dw_count_tiles(h, 0));
     L.Zi = tc_dw_z(Nb, h, tc_dw_count_tiles(c.bond_fdim, 0));
     L.Zo = tc_dw_z(Na, h, tc_dw_count_tiles(c.atom_fdim, h));
@@ -88,20 +93,22 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
   L.Pi = take(infer ? 0 : (int64_t)L.Zi * h * c.bond_fdim);
   L.Pcol = take(infer ? 0 : (int64_t)3 * kColsumMaxChunks * h);
   L.partials = L.Po;
-  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0);     // I = f_bonds W_i^T
-  L.pWh = tc_packed_geometry(h, h, 0, tc_use_gemm4() ? T4_MAX_BN : T2_MAX_BN);   // S W_h^T (gathered depth step)
-  L.pWo = tc_packed_geometry(h, c.atom_fdim, h);     // [f_atoms, A_d] W_o^T
-  L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h
+  // forward weights: the 3xTF32 mode runs all three contractions on k_tc_gemm4 (tiles up to 304 columns, hi + lo
+  // images); the single-pass mode keeps the plain ones on the TMA-fed k_tc_gemm3 (tiles up to 160 columns)
+  const int fwd_bn = x3 ? T4_MAX_BN : T2_MAX_BN, parts = x3 ? 2 : 1;
+  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0, fwd_bn, parts);     // I = f_bonds W_i^T
+  L.pWh = tc_packed_geometry(h, h, 0, T4_MAX_BN, parts);            // S W_h^T (gathered depth step)
+  L.pWo = tc_packed_geometry(h, c.atom_fdim, h, fwd_bn, parts);     // [f_atoms, A_d] W_o^T
+  L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h           (backward: single-pass TF32 in both modes)
   L.pWoT = tc_packed_geometry(h, h, 0);              // dA_d = dZo W_o[:, F_a:]
   // the message gradient only needs (y > 0) of a ReLU output: the tensor-core epilogues leave those bits behind
-  const char* sign_env = getenv("WD_SIGN_BITS");      // read per call: tests and A/B runs flip it inside one process
-  const bool sign_off = sign_env && atoi(sign_env) == 0;
+  // (decided by the config alone, so that the forward and the backward call of one step cannot disagree)
   L.sign_ld = 0;
-  if (c.math_mode == WD_MATH_TF32 && !tc_use_v1() && !infer && c.activation == WD_ACT_RELU && !sign_off)
+  if (tc && !infer && c.activation == WD_ACT_RELU && !(c.flags & WD_FLAG_NO_SIGN_BITS))
     L.sign_ld = std::max(sign_words(L.pWi), sign_words(L.pWh));
   L.Sign = take((int64_t)c.depth * Nb * L.sign_ld);
   const TcPacked* pk[5] = {&L.pWi, &L.pWh, &L.pWo, &L.pWhT, &L.pWoT};
-  for (int i = 0; i < 5; ++i) L.pk[i] = take(c.math_mode == WD_MATH_TF32 && !(infer && i >= 3) ? pk[i]->floats() : 0);
+  for (int i = 0; i < 5; ++i) L.pk[i] = take(tc && !(infer && i >= 3) ? pk[i]->floats() : 0);
   L.total = off;
   return L;
 }
@@ -114,7 +121,7 @@ int check_cfg(const WdConfig* c) {
     return fail(WD_ERR_UNSUPPORTED, "activation %d not supported (ReLU, LeakyReLU, tanh, SELU, ELU)", c->activation);
   if (c->aggregation < WD_AGG_MEAN || c->aggregation > WD_AGG_NORM)
     return fail(WD_ERR_INVALID_ARG, "aggregation %d unknown", c->aggregation);
-  if (c->math_mode != WD_MATH_FP32 && c->math_mode != WD_MATH_TF32)
+  if (c->math_mode != WD_MATH_FP32 && c->math_mode != WD_MATH_TF32 && c->math_mode != WD_MATH_TF32X3)
     return fail(WD_ERR_INVALID_ARG, "math_mode %d unknown", c->math_mode);
   if (!(c->dropout >= 0.f && c->dropout < 1.f))
     return fail(WD_ERR_INVALID_ARG, "dropout %g must be in [0, 1)", (double)c->dropout);
@@ -171,7 +178,7 @@ template <int AMODE, int BMODE, int EPI, int ACT, bool PREACT>
 int gemm(const WdConfig& c, cudaStream_t s, const AOperand& A, const float* W, int ldb, const float* bias,
          const float* R, int ldr, float* C, int ldc, int64_t M, int N, int K, const TcPacked* tc,
          const Dropout& drop = Dropout{}, const SignBits& sign = SignBits{}) {
-  if (c.math_mode == WD_MATH_TF32) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M, drop, sign);
+  if (is_tc(c)) return tc_gemm<AMODE, EPI, ACT, PREACT>(s, A, *tc, bias, R, ldr, C, ldc, M, drop, sign);
   dim3 grid((unsigned)ceil_div(M, SG_BM), (unsigned)ceil_div(std::max(N, ldc), SG_BN));
   WD_LAUNCH((k_simt_gemm<AMODE, BMODE, EPI, ACT, PREACT>), grid, SG_THREADS, 0, s, A, W, ldb, bias, R, ldr,
             C, ldc, M, N, K, drop);
@@ -182,7 +189,10 @@ int gemm(const WdConfig& c, cudaStream_t s, const AOperand& A, const float* W, i
 template <int YMODE, int ACT, bool PREACT>
 int dw_partial(const WdConfig& c, cudaStream_t s, const float* X, int ldx, const AOperand& Y, int w0, int w1,
                float* P, int64_t R, int N1, int Z) {
-  if (c.math_mode == WD_MATH_TF32) return tc_dw<YMODE, ACT, PREACT>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
+  if (is_tc(c)) {
+    if constexpr (YMODE == A_GATHER_DIFF) return fail(WD_ERR_UNSUPPORTED, "tensor-core dW reads S_t, not the gathered operand");
+    else return tc_dw<YMODE>(s, X, ldx, Y, w0, w1, P, R, N1, Z);
+  }
   const int N2 = w0 + w1;
   int64_t rpc = round_up(ceil_div(R, Z), DW_BK);
   dim3 grid((unsigned)ceil_div(N2, DW_BN), (unsigned)ceil_div(N1, DW_BM), (unsigned)Z);
@@ -193,7 +203,7 @@ int dw_partial(const WdConfig& c, cudaStream_t s, const float* X, int ldx, const
 // TF32 mode: bind the packed-weight images to the workspace and (re)pack them from the live weights
 int bind_packed(const WdConfig& c, Layout& L, void* ws) {
   TcPacked* pk[5] = {&L.pWi, &L.pWh, &L.pWo, &L.pWhT, &L.pWoT};
-  for (int i = 0; i < 5; ++i) pk[i]->img = c.math_mode == WD_MATH_TF32 ? L.p(ws, L.pk[i]) : nullptr;
+  for (int i = 0; i < 5; ++i) pk[i]->img = is_tc(c) ? L.p(ws, L.pk[i]) : nullptr;
   return WD_OK;
 }
 
@@ -259,7 +269,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
   const int64_t Na = g.n_atoms, Nb = g.n_bonds, G = g.n_mols;
   float* I = L.p(ws, L.I);
   bind_packed(c, L, ws);
-  if (c.math_mode == WD_MATH_TF32) {   // weights change every step: repack (tiny) on the stream
+  if (L.tc) {   // weights change every step: repack (tiny) on the stream
     ProfScope ps(WD_PROF_MISC);
     TcPacker pk;                       // one launch for the three forward weights
     pk.add(w.W_i, Fb, B_NK, L.pWi);
@@ -294,7 +304,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
     // message = act(input + W_h(a_message[b2a] - message[b2revb]))                   :119-123
     AOperand a_s{A_t, u, g.src, g.rev, ld, ld, 0};
     a_s.rev_adjacent = g.rev_adjacent;
-    if (c.math_mode == WD_MATH_TF32 && !tc_use_v1() && !infer) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
+    if (L.tc && !infer) a_s.S_out = L.p(ws, L.S) + (int64_t)(t - 1) * L.szB;   // kept for dW_h
     const float* bh = c.bias ? w.b_h : nullptr;
     const Dropout drop = make_dropout(c, t);                                          // :124
     const SignBits sg = sign_bits(L, ws, Nb, t, L.pWh);
@@ -357,7 +367,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
   const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim, Fo = Fa + h;
   bind_packed(c, L, ws);
-  if (c.math_mode == WD_MATH_TF32) {
+  if (L.tc) {
     ProfScope ps(WD_PROF_MISC);
     TcPacker pk;                       // one launch for the two transposed backward weights
     if (c.depth > 1) pk.add(w.W_h, h, B_KN, L.pWhT);
@@ -417,7 +427,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
     const float* u = M_prev;
     bool upre = pre;
-    const bool have_S = c.math_mode == WD_MATH_TF32 && !tc_use_v1();   // forward kept S_t (tensor-core path)
+    const bool have_S = L.tc;   // forward kept S_t (tensor-core path)
     if (c.undirected && !have_S) {
       float* U = L.p(ws, L.U);
       if (pre) WD_LAUNCH((k_symmetrize<ACT, true>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
@@ -518,6 +528,8 @@ extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weight
     return fail(WD_ERR_INVALID_ARG, "workspace/grads/d_out is NULL");
   if (workspace_bytes < wd_workspace_bytes(cfg, graph->n_atoms, graph->n_bonds, graph->n_mols))
     return fail(WD_ERR_INVALID_ARG, "workspace too small");
+  if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
+    return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
   int rc = WD_OK;
   WD_DISPATCH_ACT(cfg->activation,
                   rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, (cudaStream_t)stream));
@@ -537,8 +549,10 @@ extern "C" int wd_debug_gemm(const float* A, int lda, const float* W, int ldb, i
   cudaStream_t s = (cudaStream_t)stream;
   WdConfig c{};
   c.math_mode = math_mode;
-  TcPacked pk = tc_packed_geometry(N, K, 0);
-  if (math_mode == WD_MATH_TF32) {
+  // TF32X3: the forward kernel's geometry (tiles up to 304 columns, hi + lo weight images); b_kn is a backward form
+  const bool x3 = math_mode == WD_MATH_TF32X3 && !b_kn;
+  TcPacked pk = tc_packed_geometry(N, K, 0, x3 ? T4_MAX_BN : T2_MAX_BN, x3 ? 2 : 1);
+  if (math_mode != WD_MATH_FP32) {
     if (!scratch || scratch_bytes < (size_t)pk.floats() * sizeof(float))
       return fail(WD_ERR_INVALID_ARG, "wd_debug_gemm: scratch needs %lld bytes", (long long)pk.floats() * 4);
     pk.img = reinterpret_cast<float*>(scratch);
@@ -566,7 +580,7 @@ extern "C" int wd_debug_dw(const float* X, int ldx, const float* Y, int ldy, flo
   cudaStream_t s = (cudaStream_t)stream;
   WdConfig c{};
   c.math_mode = math_mode;
-  const int Z = math_mode == WD_MATH_TF32 ? tc_dw_z(R, N1, tc_dw_count_tiles(N2, 0)) : dw_chunks(R, N1, N2);
+  const int Z = math_mode != WD_MATH_FP32 ? tc_dw_z(R, N1, tc_dw_count_tiles(N2, 0)) : dw_chunks(R, N1, N2);
   if (!scratch || scratch_bytes < (size_t)Z * N1 * N2 * sizeof(float))
     return fail(WD_ERR_INVALID_ARG, "wd_debug_dw: scratch needs %lld bytes", (long long)Z * N1 * N2 * 4);
   float* P = reinterpret_cast<float*>(scratch);

@@ -1,6 +1,7 @@
-// tcgen05 weight-gradient contraction, fourth generation: MN-major operands, no transpose.
+// tcgen05 weight-gradient contraction with cp.async loaders: MN-major operands, no transpose.  The fallback of
+// tc_dw5.cuh for Y rows that are only 4-byte aligned (dense 133 / 147-float feature rows).
 //
-//   P[z][n1, n2] = sum_{r in chunk z} X[r, n1] * Y(r, n2),   Y(r, :) = Y0[i0(r), :] - act?(Y1[i1(r), :])
+//   P[z][n1, n2] = sum_{r in chunk z} X[r, n1] * Y[r, n2]
 //
 // The reduction runs over ROWS, so in the row-major activations the M / N index of both operands is the
 // contiguous one: exactly the tensor core's MN-major operand form.  Generations 2 and 3 transposed every
@@ -8,13 +9,12 @@
 // showed those transform warps 95 % busy and everything else waiting on them.  Here
 //   loaders    cp.async 16-byte pieces of raw rows straight into the MN-major operand stage
 //              (SWIZZLE_128B_BASE32B: 8 rows x 128 bytes per 32-column block, blocks 1 KB apart),
-//   transform  rounds to TF32 IN PLACE (and folds the subtrahend source for the gather operand): pure
-//              16-byte elementwise traffic, no address arithmetic, no second ring,
+//   transform  rounds to TF32 IN PLACE: pure 16-byte elementwise traffic, no address arithmetic, no second ring,
 //   MMA        tcgen05.mma kind::tf32 with a_major = b_major = MN, up to three M=128 accumulators,
 //   epilogue   the first four transform warps, once, after the last chunk.
 // One CTA owns up to 384 X columns x one Y tile of <= 160 columns x one row chunk z (as generation 3).
 #pragma once
-#include "tc_dw3.cuh"
+#include "tc_core.cuh"
 
 namespace wd {
 
@@ -35,11 +35,8 @@ struct D4Barriers {
 struct D4Params {
   const float* X;       // [R, ldx], 16-byte aligned rows
   int ldx, N1;
-  const float* Y0[2];
-  const float* Y1;
-  const int32_t* i0;
-  const int32_t* i1;
-  int ldy[2], ldy1;
+  const float* Y0[2];   // Y segments (CONCAT: two)
+  int ldy[2];
   int align16[2];
   float* P;             // [Z][N1, ldp]
   int ldp;
@@ -50,9 +47,9 @@ struct D4Params {
   TcDwTile t[TC_DW_MAX_TILES];
 };
 
-inline int d4_stage_bytes(int XB, int YB, int nsrc) { return (2 * XB + nsrc * 2 * YB) * 1024; }
-inline int d4_smem_bytes(int XB, int YB, int nsrc, int stages) {
-  return 1024 + stages * d4_stage_bytes(XB, YB, nsrc) + TC_EPI_STAGE_BYTES + (int)sizeof(D4Barriers) + 64;
+inline int d4_stage_bytes(int XB, int YB) { return (2 * XB + 2 * YB) * 1024; }
+inline int d4_smem_bytes(int XB, int YB, int stages) {
+  return 1024 + stages * d4_stage_bytes(XB, YB) + TC_EPI_STAGE_BYTES + (int)sizeof(D4Barriers) + 64;
 }
 
 // MN-major descriptor for 32-bit operands.  The only MN-major layout the tensor core accepts for tf32 is
@@ -105,7 +102,6 @@ __device__ __forceinline__ void d4_epilogue(uint32_t tmem_acc, int we, int lane,
   }
 }
 
-template <int NSRC, int ACT, bool PREACT>
 __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   extern __shared__ uint8_t smem_raw[];
@@ -113,7 +109,7 @@ __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
   const uint32_t base = ptx::smem_u32(smem_raw);
   uint8_t* ring = smem_raw + (((base + 1023u) & ~1023u) - base);        // 1024-aligned: swizzle atoms
   const int XB = p.XB, YB = p.YB, SR = p.stages;
-  const int x_bytes = 2 * XB * 1024, y_bytes = 2 * YB * 1024, stage_bytes = x_bytes + NSRC * y_bytes;
+  const int x_bytes = 2 * XB * 1024, y_bytes = 2 * YB * 1024, stage_bytes = x_bytes + y_bytes;
   float* epi_st = reinterpret_cast<float*>(ring + SR * stage_bytes);
   D4Barriers* bar = reinterpret_cast<D4Barriers*>(ring + SR * stage_bytes + TC_EPI_STAGE_BYTES);
   long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // WD_T2_TIMING: 0 xform<-raw_full 2 loader<-empty 5 mma<-op_full
@@ -155,7 +151,6 @@ __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
       T2_WAIT(0, &bar->raw_full[s], (kc / SR) & 1);
       float4* sx = reinterpret_cast<float4*>(ring + s * stage_bytes);
       float4* sy = reinterpret_cast<float4*>(ring + s * stage_bytes + x_bytes);
-      const float4* sy1 = reinterpret_cast<const float4*>(ring + s * stage_bytes + x_bytes + y_bytes);
       for (int i0 = t; i0 < xp; i0 += 4 * D4_XFORM_THREADS) {
         float4 v[4];
 #pragma unroll
@@ -166,20 +161,13 @@ __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
             sx[i0 + j * D4_XFORM_THREADS] = make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
       }
       for (int i0 = t; i0 < yp; i0 += 2 * D4_XFORM_THREADS) {
-        float4 v[2], u[2];
+        float4 v[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+          if (i0 + j * D4_XFORM_THREADS < yp) v[j] = sy[i0 + j * D4_XFORM_THREADS];
 #pragma unroll
         for (int j = 0; j < 2; ++j)
           if (i0 + j * D4_XFORM_THREADS < yp) {
-            v[j] = sy[i0 + j * D4_XFORM_THREADS];
-            if (NSRC == 2) u[j] = sy1[i0 + j * D4_XFORM_THREADS];
-          }
-#pragma unroll
-        for (int j = 0; j < 2; ++j)
-          if (i0 + j * D4_XFORM_THREADS < yp) {
-            if (NSRC == 2) {
-              if (PREACT) u[j] = f4_act<ACT>(u[j]);
-              v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
-            }
             sy[i0 + j * D4_XFORM_THREADS] = make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
           }
       }
@@ -207,16 +195,14 @@ __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
     const float* Y0 = p.Y0[seg];
     const int ldy = p.ldy[seg];
     const bool al = p.align16[seg] != 0;
-    const bool indirect = (seg == 0) && p.i0 != nullptr;
     const int xblocks = (int)ceil_div(n1_w, 32), yblocks = (int)ceil_div(tl.width, 32);
     for (int kc = 0; kc < KC; ++kc) {
       const int s = kc % SR;
       const int64_t r = r_begin + (int64_t)kc * D4_BK + rl;
       const bool ok = r < r_end;
-      int64_t ra = ok ? r : 0, rb = ra;
-      if (ok && indirect) { ra = __ldg(p.i0 + r); if (NSRC == 2) rb = __ldg(p.i1 + r); }
+      int64_t ra = ok ? r : 0;
       const int64_t rx = (WD_ABL & 2) ? (r & 2047) : r;         // timing ablation: rows from an L2-resident window
-      if (WD_ABL & 2) { ra &= 2047; rb &= 2047; }
+      if (WD_ABL & 2) ra &= 2047;
       T2_WAIT(2, &bar->empty[s], ((kc / SR) & 1) ^ 1);
       if (WD_ABL & 32) { ptx::cp_async_arrive(&bar->raw_full[s]); continue; }
       const uint32_t dx = ring_u32 + s * stage_bytes + kg * XB * 1024 + piece;
@@ -230,13 +216,11 @@ __global__ void __launch_bounds__(D4_THREADS, 1) k_tc_dw4(const D4Params p) {
       }
       if (al) {
         const float* y0row = Y0 + ra * ldy + tl.col0 + q8 * 4;
-        const float* y1row = NSRC == 2 ? p.Y1 + rb * p.ldy1 + tl.col0 + q8 * 4 : nullptr;
         for (int b = 0; b < yblocks; ++b) {
           const int rem = (tl.width - (b * 32 + q8 * 4)) * 4;
           if (rem <= 0) break;
           const uint32_t v = !ok ? 0u : (rem >= 16 ? 16u : (uint32_t)rem);
           ptx::cp_async16(dy + b * 1024, v ? y0row + b * 32 : Y0, v);
-          if (NSRC == 2) ptx::cp_async16(dy + y_bytes + b * 1024, v ? y1row + b * 32 : p.Y1, v);
         }
       } else {  // rows only 4-byte aligned (dense 133 / 147-float feature rows): 4-byte copies
         const float* y0row = Y0 + ra * ldy + tl.col0;

@@ -1,16 +1,17 @@
-// tcgen05 weight-gradient contraction, fifth generation: TMA-fed MN-major operands.
+// tcgen05 weight-gradient contraction: TMA-fed MN-major operands.
 //
-//   P[z][n1, n2] = sum_{r in chunk z} X[r, n1] * Y(r, n2),   Y(r, :) = Y0[i0(r), :] - act?(Y1[i1(r), :])
+//   P[z][n1, n2] = sum_{r in chunk z} X[r, n1] * Y[r, n2]
 //
 // What the wait-cycle counters and the ablations of generation 4 said (profiles/r1_g_*): the kernel was bound by
 // work done ON the SM, not by HBM or L2 -- LDGSTS (cp.async) moves 16 bytes per cycle per SM at best, and the
 // in-place rounding pass pushed every operand byte through shared memory two more times.  Here
-//   * X (always a plain matrix) and a plain Y arrive by TMA tensor copies (cp.async.bulk.tensor, boxes of
-//     BK rows x 32 columns) written straight into the MN-major SWIZZLE_128B_BASE32B operand layout, the
-//     tensor map's TFLOAT32 data type making the TMA engine round fp32 -> tf32 in flight: no loader
-//     instructions, no transform pass, no proxy fence -- TMA -> mbarrier -> tcgen05.mma;
-//   * only the gathered Y of dW_h (two indexed sources, subtracted) still uses cp.async + an in-place transform.
-// Tiling as generations 3/4: one CTA = up to 384 X columns x one Y tile of <= 160 columns x one row chunk z.
+//   * X and Y arrive by TMA tensor copies (cp.async.bulk.tensor, boxes of BK rows x 32 columns) written straight
+//     into the MN-major SWIZZLE_128B_BASE32B operand layout, the tensor map's TFLOAT32 data type making the TMA
+//     engine round fp32 -> tf32 in flight: no loader instructions, no transform pass, no proxy fence --
+//     TMA -> mbarrier -> tcgen05.mma;
+//   * the gathered operand of dW_h (S_t = a_message[b2a] - message[b2revb]) is a plain matrix too: the forward
+//     depth step leaves it in the workspace (tc_gemm4.cuh).
+// Tiling as tc_dw4.cuh: one CTA = up to 384 X columns x one Y tile of <= 160 columns x one row chunk z.
 #pragma once
 #include "tc_dw4.cuh"
 #include "tc_tma.cuh"
@@ -18,25 +19,19 @@
 namespace wd {
 
 constexpr int D5_MAX_STAGES = 6;
-constexpr int D5_MMA_WARP = 0, D5_TMA_WARP = 1, D5_LOAD_W0 = 2, D5_LOAD_WARPS = 4, D5_XFORM_W0 = 6, D5_XFORM_WARPS = 8;
-constexpr int D5_LOAD_THREADS = 32 * D5_LOAD_WARPS, D5_XFORM_THREADS = 32 * D5_XFORM_WARPS;
-__host__ __device__ constexpr int d5_bk(int nsrc) { return nsrc == 1 ? 32 : 16; }                 // rows per stage
-__host__ __device__ constexpr int d5_threads(int nsrc) { return nsrc == 1 ? 32 * D5_XFORM_W0 : 32 * (D5_XFORM_W0 + D5_XFORM_WARPS); }
+constexpr int D5_MMA_WARP = 0, D5_TMA_WARP = 1, D5_EPI_W0 = 2;
+constexpr int D5_BK = 32;                       // rows per stage
+constexpr int D5_THREADS = 32 * (D5_EPI_W0 + 4);
 
 struct D5Barriers {
-  uint64_t full[D5_MAX_STAGES], raw_full[D5_MAX_STAGES], op_full[D5_MAX_STAGES], empty[D5_MAX_STAGES];
+  uint64_t full[D5_MAX_STAGES], empty[D5_MAX_STAGES];
   uint64_t tmem_full;
   uint32_t tmem_base;
 };
 
 struct D5Params {
   CUtensorMap mx;       // X[R, N1], box BK x 32
-  CUtensorMap my[2];    // plain Y segments (unused for the gathered operand)
-  const float* Y0;      // gathered operand: minuend rows / subtrahend rows and their row maps
-  const float* Y1;
-  const int32_t* i0;
-  const int32_t* i1;
-  int ldy0, ldy1;
+  CUtensorMap my[2];    // Y segments (CONCAT: two), box BK x 32
   int N1;
   float* P;             // [Z][N1, ldp]
   int ldp;
@@ -46,33 +41,27 @@ struct D5Params {
   TcDwTile t[TC_DW_MAX_TILES];
 };
 
-inline int d5_stage_bytes(int XB, int YB, int nsrc) { return (XB + nsrc * YB) * d5_bk(nsrc) * 128; }
-inline int d5_smem_bytes(int XB, int YB, int nsrc, int stages) {
-  return 1024 + stages * d5_stage_bytes(XB, YB, nsrc) + TC_EPI_STAGE_BYTES + (int)sizeof(D5Barriers) + 64;
+inline int d5_stage_bytes(int XB, int YB) { return (XB + YB) * D5_BK * 128; }
+inline int d5_smem_bytes(int XB, int YB, int stages) {
+  return 1024 + stages * d5_stage_bytes(XB, YB) + TC_EPI_STAGE_BYTES + (int)sizeof(D5Barriers) + 64;
 }
 
-template <int NSRC, int ACT, bool PREACT>
-__global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_constant__ D5Params p) {
+__global__ void __launch_bounds__(D5_THREADS, 1) k_tc_dw5(const __grid_constant__ D5Params p) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
-  constexpr int BK = d5_bk(NSRC), BLK = BK * 128;                             // bytes of one 32-column block
+  constexpr int BK = D5_BK, BLK = BK * 128;                                   // bytes of one 32-column block
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);
   uint8_t* ring = smem_raw + (((base + 1023u) & ~1023u) - base);
   const int XB = p.XB, YB = p.YB, SR = p.stages;
-  const int x_bytes = XB * BLK, y_bytes = YB * BLK, stage_bytes = x_bytes + NSRC * y_bytes;
+  const int x_bytes = XB * BLK, y_bytes = YB * BLK, stage_bytes = x_bytes + y_bytes;
   float* epi_st = reinterpret_cast<float*>(ring + SR * stage_bytes);
   D5Barriers* bar = reinterpret_cast<D5Barriers*>(ring + SR * stage_bytes + TC_EPI_STAGE_BYTES);
-  long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // WD_T2_TIMING: 0 xform<-raw_full 2 loader<-empty 3 tma<-empty
-  const long long t_start = clock64();                   //               5 mma<-full 6 mma<-op_full 7 epi<-tmem_full
+  long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // WD_T2_TIMING: 3 tma<-empty 5 mma<-full 7 epi<-tmem_full
+  const long long t_start = clock64();
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < SR; ++s) {
-      ptx::mbar_init(&bar->full[s], 1);
-      ptx::mbar_init(&bar->raw_full[s], D5_LOAD_THREADS);
-      ptx::mbar_init(&bar->op_full[s], D5_XFORM_WARPS);
-      ptx::mbar_init(&bar->empty[s], 1);
-    }
+    for (int s = 0; s < SR; ++s) { ptx::mbar_init(&bar->full[s], 1); ptx::mbar_init(&bar->empty[s], 1); }
     ptx::mbar_init(&bar->tmem_full, 1);
     ptx::fence_barrier_init();
     ptx::tma_prefetch_desc(&p.mx);
@@ -99,7 +88,6 @@ __global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_con
     for (int kc = 0; kc < KC; ++kc) {
       const int s = kc % SR;
       T2_WAIT(5, &bar->full[s], (kc / SR) & 1);
-      if (NSRC == 2) T2_WAIT(6, &bar->op_full[s], (kc / SR) & 1);
       ptx::tc_fence_after();
       if (lane == 0) {
         const uint32_t xa = ring_u32 + s * stage_bytes, ya = xa + x_bytes;
@@ -116,10 +104,10 @@ __global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_con
       __syncwarp();
     }
   } else if (warp == D5_TMA_WARP) {
-    // ================= TMA producer: X boxes (and the plain Y boxes) of every stage =================
+    // ================= TMA producer: X and Y boxes of every stage =================
     if (lane == 0) {
       const CUtensorMap* my = &p.my[tl.seg];
-      const uint32_t bytes = (uint32_t)((xblocks + (NSRC == 1 ? yblocks : 0)) * BLK);
+      const uint32_t bytes = (uint32_t)((xblocks + yblocks) * BLK);
       for (int kc = 0; kc < KC; ++kc) {
         const int s = kc % SR;
         const int r0 = (int)(r_begin + (int64_t)kc * BK);
@@ -127,36 +115,10 @@ __global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_con
         ptx::mbar_arrive_expect_tx(&bar->full[s], bytes);
         uint8_t* xs = ring + s * stage_bytes;
         for (int b = 0; b < xblocks; ++b) ptx::tma_load_2d(xs + b * BLK, &p.mx, n1_0 + b * 32, r0, &bar->full[s]);
-        if (NSRC == 1)
-          for (int b = 0; b < yblocks; ++b) ptx::tma_load_2d(xs + x_bytes + b * BLK, my, tl.col0 + b * 32, r0, &bar->full[s]);
+        for (int b = 0; b < yblocks; ++b) ptx::tma_load_2d(xs + x_bytes + b * BLK, my, tl.col0 + b * 32, r0, &bar->full[s]);
       }
     }
-  } else if (warp < D5_XFORM_W0) {
-    // ================= gather loaders (dW_h): 8 threads per row, cp.async into the swizzled Y blocks =================
-    if (NSRC == 2) {
-      const int t = threadIdx.x - 32 * D5_LOAD_W0, rl = t >> 3, q8 = t & 7;
-      const uint32_t ring_u32 = ptx::smem_u32(ring);
-      const uint32_t piece = (uint32_t)(rl * 128 + ((q8 ^ ((rl & 3) << 1)) << 4));
-      for (int kc = 0; kc < KC; ++kc) {
-        const int s = kc % SR;
-        const int64_t r = r_begin + (int64_t)kc * BK + rl;
-        const bool ok = r < r_end;
-        int64_t ra = 0, rb = 0;
-        if (ok) { ra = p.i0 ? __ldg(p.i0 + r) : r; rb = p.i1 ? __ldg(p.i1 + r) : r; }
-        T2_WAIT(2, &bar->empty[s], ((kc / SR) & 1) ^ 1);
-        const uint32_t dy = ring_u32 + s * stage_bytes + x_bytes + piece;
-        const float* y0row = p.Y0 + ra * p.ldy0 + tl.col0 + q8 * 4;
-        const float* y1row = p.Y1 + rb * p.ldy1 + tl.col0 + q8 * 4;
-        for (int b = 0; b < yblocks; ++b) {
-          const int rem = (tl.width - (b * 32 + q8 * 4)) * 4;
-          if (rem <= 0) break;
-          const uint32_t v = !ok ? 0u : (rem >= 16 ? 16u : (uint32_t)rem);
-          ptx::cp_async16(dy + b * BLK, v ? y0row + b * 32 : p.Y0, v);
-          ptx::cp_async16(dy + y_bytes + b * BLK, v ? y1row + b * 32 : p.Y1, v);
-        }
-        ptx::cp_async_arrive(&bar->raw_full[s]);
-      }
-    }
+  } else {
     // ================= epilogue: warps 2-5, TMEM lane quarter = warp % 4 =================
     T2_WAIT(7, &bar->tmem_full, 0);
     ptx::tc_fence_after();
@@ -165,38 +127,12 @@ __global__ void __launch_bounds__(d5_threads(NSRC), 1) k_tc_dw5(const __grid_con
     for (int mt = 0; mt < n_mt; ++mt)
       d4_epilogue(tmem_base + mt * D4_ACC_COLS, we, lane, epi_st + we * 32 * 33, tl.BN, n1_0 + mt * TC_BM, p.N1,
                   tl.out_col0, tl.out_col0 + tl.width, Pz, p.ldp);
-  } else {
-    // ================= transform (dW_h): Y <- tf32(Y0 - act(Y1)) in place =================
-    const int t = threadIdx.x - 32 * D5_XFORM_W0;
-    const int yp = y_bytes / 16;
-    for (int kc = 0; kc < KC; ++kc) {
-      const int s = kc % SR;
-      T2_WAIT(0, &bar->raw_full[s], (kc / SR) & 1);
-      float4* sy = reinterpret_cast<float4*>(ring + s * stage_bytes + x_bytes);
-      const float4* sy1 = reinterpret_cast<const float4*>(ring + s * stage_bytes + x_bytes + y_bytes);
-      for (int i0 = t; i0 < yp; i0 += 3 * D5_XFORM_THREADS) {
-        float4 v[3], u[3];
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-          if (i0 + j * D5_XFORM_THREADS < yp) { v[j] = sy[i0 + j * D5_XFORM_THREADS]; u[j] = sy1[i0 + j * D5_XFORM_THREADS]; }
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-          if (i0 + j * D5_XFORM_THREADS < yp) {
-            if (PREACT) u[j] = f4_act<ACT>(u[j]);
-            sy[i0 + j * D5_XFORM_THREADS] = make_float4(ptx::to_tf32(v[j].x - u[j].x), ptx::to_tf32(v[j].y - u[j].y),
-                                                        ptx::to_tf32(v[j].z - u[j].z), ptx::to_tf32(v[j].w - u[j].w));
-          }
-      }
-      ptx::fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&bar->op_full[s]);
-    }
   }
 #ifdef WD_T2_TIMING
   if (WD_TIMING_ON(15) && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) {
-    if (warp == D5_MMA_WARP || warp == D5_TMA_WARP || warp == D5_LOAD_W0 || warp == D5_XFORM_W0)
+    if (warp == D5_MMA_WARP || warp == D5_TMA_WARP || warp == D5_EPI_W0)
       for (int i = 0; i < 10; ++i) if (tacc[i]) atomicAdd(&g_t2_timing[i], (unsigned long long)tacc[i]);
-    if (warp == D5_LOAD_W0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));
+    if (warp == D5_EPI_W0) atomicAdd(&g_t2_timing[15], (unsigned long long)(clock64() - t_start));
   }
 #else
   (void)tacc; (void)t_start;

@@ -1,19 +1,27 @@
-// tcgen05 contraction kernel, third generation, for PLAIN / CONCAT A operands (no gather):
+// tcgen05 contraction kernel for PLAIN / CONCAT A operands (no gather), single-pass TF32:
 //
 //   C[M, ldc] = epi( A * B^T ),  A = [X0 | X1] row-major matrices with 16-byte aligned rows
 //
-// The second generation moved every A byte with cp.async (LDGSTS: measured ~12 bytes / cycle / SM, the binding
+// An earlier generation moved every A byte with cp.async (LDGSTS: measured ~12 bytes / cycle / SM, the binding
 // limit once the epilogue was fixed) and then through a transform pass (round to TF32, swizzle).  A plain
 // matrix needs neither: a TMA tensor copy (box 128 rows x 32 columns, SWIZZLE_128B) writes the K-major operand
 // stage directly and its TFLOAT32 data type rounds fp32 -> tf32 in flight.  One producer lane issues the A box
 // and the bulk copy of the packed weight chunk on one mbarrier; tcgen05.mma consumes it; the epilogue
-// (t2_epilogue) overlaps the next tile through the second TMEM accumulator.
+// overlaps the next tile through the second TMEM accumulator.
 //   warps 0-3 epilogue, warp 4 MMA issue, warp 5 producer.
+// Used by the backward pass (dS = dZ W_h, dA = dZo W_o[:, F_a:]) in every tensor-core mode and by the forward input
+// projection / atom update in the single-pass TF32 mode (the 3xTF32 mode needs the raw fp32 operand: tc_gemm4.cuh).
 #pragma once
-#include "tc_gemm2.cuh"
+#include "tc_core.cuh"
 #include "tc_tma.cuh"
 
 namespace wd {
+
+constexpr int T2_EPI_WARPS = 4, T2_MMA_WARP = 4;
+constexpr int T2_MAX_BN = 160;                    // two accumulators in TMEM: epilogue overlaps the next tile
+constexpr int T2_R_SLOTS = 3, T2_R_ROW = 144;     // transpose staging: 128 rows x 32 floats, rows padded to 144 B
+constexpr int T2_R_SLOT_BYTES = TC_BM * T2_R_ROW;
+constexpr int T2_R_BYTES = T2_R_SLOTS * T2_R_SLOT_BYTES;
 
 constexpr int T3_STAGES = 4;
 constexpr int T3_PROD_WARP = 5;
@@ -22,7 +30,6 @@ constexpr int T3_THREADS = 32 * 6;
 struct T3Barriers {
   uint64_t full[T3_STAGES], empty[T3_STAGES];
   uint64_t tmem_full[2], tmem_empty[2];
-  uint64_t r_dummy[2 * T2_R_SLOTS];   // t2_epilogue's residual barriers (unused: EPI != E_RES_ACT here)
   uint32_t tmem_base;
 };
 
@@ -40,7 +47,62 @@ struct T3Params {
 };
 
 inline int t3_smem_bytes(int BN) {
-  return 1024 + T3_STAGES * (TC_A_STAGE + BN * 128) + T2_R_BYTES + (int)sizeof(T2Barriers) + (int)sizeof(T3Barriers) + 64;
+  return 1024 + T3_STAGES * (TC_A_STAGE + BN * 128) + T2_R_BYTES + (int)sizeof(T3Barriers) + 64;
+}
+
+// Epilogue of one 128 x BN accumulator, 32 columns at a time.  The row-owning thread parks its accumulator row in
+// a staging slot (conflict-free 16-byte accesses: rows are 144 bytes apart), then the warp writes the 32 rows out
+// with 8 lanes per row (16 bytes each, 4 rows per instruction -> full 128-byte lines), applying bias + activation.
+template <int EPI, int ACT>
+__device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, uint32_t& rit, int BN,
+                                            int64_t row0, int64_t M, int col0, int N, int cmax, const float* bias,
+                                            float* C, int ldc, const Dropout& drop, const SignBits& sign) {
+  uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
+  for (int c0 = 0; c0 < BN; c0 += 32, ++rit) {
+    const int slot = rit % T2_R_SLOTS;
+    uint8_t* sl = rring + slot * T2_R_SLOT_BYTES + (we * 32) * T2_R_ROW;     // this warp's 32 rows
+    float v[32];
+    const uint32_t ta = tmem_acc + ((uint32_t)(we * 32) << 16) + (uint32_t)c0;
+    if (BN - c0 >= 32) {
+      ptx::tmem_ld32(ta, v);
+    } else {
+      ptx::tmem_ld16(ta, v);
+#pragma unroll
+      for (int j = 16; j < 32; ++j) v[j] = 0.f;
+    }
+    ptx::tmem_ld_wait();
+    float4* myrow = reinterpret_cast<float4*>(sl + lane * T2_R_ROW);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) myrow[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncwarp();
+    const int pc = lane & 7, rq = lane >> 3;
+    const int colb = col0 + c0 + pc * 4;
+    const int nval = (c0 + pc * 4 < BN) ? max(0, min(4, N - colb)) : 0;      // live columns of this piece
+    const bool in_c = colb < cmax && c0 + pc * 4 < BN;
+    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (bias != nullptr) {
+      if (nval > 0) bv.x = __ldg(bias + colb);
+      if (nval > 1) bv.y = __ldg(bias + colb + 1);
+      if (nval > 2) bv.z = __ldg(bias + colb + 2);
+      if (nval > 3) bv.w = __ldg(bias + colb + 3);
+    }
+    float4 xv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) xv[i] = *reinterpret_cast<const float4*>(sl + (rq + 4 * i) * T2_R_ROW + pc * 16);
+    float* cp = C + (row0 + we * 32 + rq) * ldc + colb;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
+      if (EPI != E_STORE) x = f4_act<ACT>(x);
+      if (EPI != E_STORE && drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
+      if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
+      const bool ok = in_c && row0 + we * 32 + rq + 4 * i < M && !(WD_ABL & 4);
+      if (ok) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
+      if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
+    }
+    __syncwarp();
+  }
+  if (sign.p != nullptr) sign_flush(sign, sw, col0 / BN, row0 + we * 32, M, lane >> 3, lane & 7, (BN + 31) >> 5);
 }
 
 template <int EPI, int ACT>
@@ -53,8 +115,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
   uint8_t* ops = smem_raw + (((base + 1023u) & ~1023u) - base);        // 1024-aligned
   const int b_stage = p.BN * 128, stage = TC_A_STAGE + b_stage;          // multiples of 1024 (BN % 16 == 0 -> 2048)
   uint8_t* rring = ops + T3_STAGES * stage;
-  T2Barriers* ebar = reinterpret_cast<T2Barriers*>(rring + T2_R_BYTES);  // only handed to t2_epilogue
-  T3Barriers* bar = reinterpret_cast<T3Barriers*>(ebar + 1);
+  T3Barriers* bar = reinterpret_cast<T3Barriers*>(rring + T2_R_BYTES);
   long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // WD_T2_TIMING: 3 producer<-empty 4 mma<-tmem_empty 5 mma<-full 7 epi<-tmem_full
   const long long t_start = clock64();
 
@@ -118,8 +179,8 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
       const int col0 = (int)(tile % p.n_tiles) * p.BN;
       T2_WAIT(7, &bar->tmem_full[acc], (tl >> 1) & 1);
       ptx::tc_fence_after();
-      t2_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, ebar, rit, p.BN, row0, p.M, col0, p.N, p.ldc,
-                            p.bias, p.C, p.ldc, tacc, p.drop, p.sign);
+      t3_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, rit, p.BN, row0, p.M, col0, p.N, p.ldc, p.bias,
+                            p.C, p.ldc, p.drop, p.sign);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);

@@ -1,6 +1,9 @@
-// tcgen05 contraction kernel for the GATHERED depth step, fourth generation:
+// tcgen05 FORWARD contraction kernel (fourth generation): every forward contraction of the encoder that needs the
+// raw fp32 operand on the SM -- the gathered depth step in every tensor-core mode, and all three forward
+// contractions in the 3xTF32 mode --
 //
-//   C[M, ldc] = act( R + (X0[i0(r), :] - act?(X1[i1(r), :])) * B^T + bias )       (mpn.py:119-123 as one kernel)
+//   GATHER : C[M, ldc] = act( R + (X0[i0(r), :] - act?(X1[i1(r), :])) * B^T + bias )     (mpn.py:119-123 as one kernel)
+//   PLAIN  : C[M, ldc] = epi( [Xa | Xb] * B^T + bias )                                   (mpn.py:96, :132-133)
 //
 // Measured on the second generation (profiles/r1_g_*): cp.async (LDGSTS) moves ~12 bytes / cycle / SM and is the
 // binding limit; with two column tiles of 160 every gathered row was fetched twice, and the residual tile
@@ -8,18 +11,33 @@
 //   * one CTA tile spans up to 304 output columns (two accumulator halves of <= 160), so each gathered row is
 //     fetched ONCE; three 160-column TMEM buffers rotate (tile i: buffers 2i, 2i+1 mod 3), the epilogue of
 //     tile i overlaps the main loop of tile i+1;
-//   * loaders cp.async the two gathered sources straight to their SWIZZLE_128B positions; the transform warps
-//     subtract / activate / round to TF32 IN PLACE (no second operand ring) and, for the first column tile,
-//     write the operand rows S out for the weight-gradient pass (after the hand-off to the MMA);
+//   * loaders cp.async the two gathered sources straight to their SWIZZLE_128B positions (PLAIN: one TMA box,
+//     FLOAT32 map, no rounding in flight); the transform warps subtract / activate / round to TF32 IN PLACE (no
+//     second operand ring) and, for the first column tile, write the operand rows S out for the weight-gradient
+//     pass (after the hand-off to the MMA);
 //   * the residual tile arrives by TMA (FLOAT32 map, SWIZZLE_128B) in a ring that doubles as the epilogue's
-//     transpose staging; the packed weight chunk [BN x 128 B] by bulk copy;
+//     transpose staging; the packed weight chunk by bulk copies, one per accumulator half;
 //   * reverse bonds are ADJACENT PAIRS in every graph the reference builds (b1 = n_bonds, b2 = b1 + 1,
 //     featurization.py:470-480 and :616-629; with the padding bond 0 that is rev(b) = ((b-1)^1)+1).  When
 //     wd_csr_build found that to hold for the whole batch (flags[2] == 0 -> WdGraph.rev_adjacent), the rows
 //     X1[i1(r)] of a 128-row tile all lie in rows [row0-1, row0+129) of X1: ONE TMA box of 132 rows replaces
 //     128 gathered cp.async rows, i.e. half of the LDGSTS traffic that bounds this kernel, and the transform
 //     warps read the partner row of the box instead of their own.  Any other graph takes the cp.async path.
-//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 gather loaders, 11-14 transform.
+//
+// 3xTF32 (T4Params.split, math mode WD_MATH_TF32X3).  Single-pass TF32 rounds both operands to 11 significant bits
+// (2^-11 relative per element): 3.6e-4 on the encoder output and 5e-4 on predictions, above the 1e-4 bound.  With
+//   a = a_hi + a_lo,  a_hi = tf32(a), a_lo = a - a_hi           (the transform warps already touch every element)
+//   w = w_hi + w_lo                                              (k_tc_pack_b leaves both images, tc_core.cuh)
+//   a w ~= a_hi w_hi + (a_lo w_hi + a_hi w_lo)                   (all into the SAME TMEM accumulator)
+// the dropped term is ~2^-22 and the result is fp32-grade (2e-6 against fp64 at K = 300; what remains is the
+// tensor core's own accumulation rounding, which grows with K).  The correction terms are 2^-11 of the product, so
+// THEY only need 8 significant bits: they run as ONE kind::f16 (bf16 inputs) MMA group over "correction images"
+// [bf16 a_lo | bf16 a_hi] and [bf16 w_hi | bf16 w_lo] -- K = 64 bf16 in the same 128-byte rows, 4 instructions per
+// chunk instead of 8: the ablations (profiles/r2_fwd_ab.log) showed the kernel paced by the number of MMAs issued,
+// not by the weight traffic.  No extra HBM pass: the correction image of A is written over the subtrahend part of
+// the SAME smem stage (after a named barrier among the transform warps when that part holds the shared TMA box);
+// the weight ring streams two images per chunk from L2.
+//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 operand loaders, 11-14 transform.
 #pragma once
 #include "tc_gemm3.cuh"
 
@@ -32,41 +50,46 @@ constexpr int T4_MMA_WARP = 4, T4_B_WARP = 5, T4_R_WARP = 6, T4_LOAD_W0 = 7, T4_
               T4_XFORM_WARPS = WD_T4_XFORM_WARPS;
 constexpr int T4_XR = 4 * T4_XFORM_WARPS, T4_XJ = TC_BM / T4_XR;   // transform: rows per pass / passes per chunk
 constexpr int T4_THREADS = 32 * (T4_XFORM_W0 + T4_XFORM_WARPS);
-constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_R_SLOTS = 3;
+constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_B_SLOTS = 2 * T4_B_STAGES, T4_R_SLOTS = 3;
 constexpr int T4_X1_ROWS = 132, T4_X1_LEAD = 2;   // TMA box of the subtrahend rows: [row0 - 2, row0 + 130)
 constexpr int T4_X1_STAGE = 17 * 1024;            // >= T4_X1_ROWS * 128 bytes, keeps the stages 1024-byte aligned
-constexpr int T4_A_STAGE = TC_A_STAGE + T4_X1_STAGE;   // minuend rows (128 x 128 bytes, gathered) + subtrahend rows
+constexpr int T4_A_STAGE = TC_A_STAGE + T4_X1_STAGE;   // minuend rows / a_hi (128 x 128 bytes) + subtrahend rows / a_lo
 constexpr int T4_R_SLOT = TC_BM * 128;            // residual / staging slot: 128 rows x 32 floats, swizzled
 constexpr int T4_HALF = 160, T4_MAX_BN = 304;     // accumulator half / widest column tile
 static_assert(T4_LOAD_WARPS * 32 == TC_BM && (T4_XFORM_WARPS == 4 || T4_XFORM_WARPS == 8), "8 threads per row");
 
 struct T4Barriers {
   uint64_t raw_full[T4_A_STAGES], op_full[T4_A_STAGES], a_empty[T4_A_STAGES];
-  uint64_t b_full[T4_B_STAGES], b_empty[T4_B_STAGES];
+  uint64_t b_full[T4_B_SLOTS], b_empty[T4_B_SLOTS];
   uint64_t r_full[T4_R_SLOTS], r_empty[T4_R_SLOTS];
   uint64_t tmem_full[3], tmem_empty[3];
   uint32_t tmem_base;
 };
 
 struct T4Params {
-  CUtensorMap mr;       // residual R[M, N] (FLOAT32, box 128 x 32, SWIZZLE_128B)
-  const float* X0;      // minuend rows   (row map i0)
-  const float* X1;      // subtrahend rows (row map i1)
+  CUtensorMap mr;       // residual R[M, N] (FLOAT32, box 128 x 32, SWIZZLE_128B); EPI == E_RES_ACT
+  CUtensorMap mx1;      // GATHER: X1[M, K] (FLOAT32, box 132 rows x 32 columns, SWIZZLE_128B), used when x1_tma != 0
+  CUtensorMap ma[2];    // PLAIN: the K segments of A (FLOAT32, box 128 x 32, SWIZZLE_128B), used when a_tma != 0
+  const float* X0;      // GATHER: minuend rows (row map i0).  PLAIN: first K segment
+  const float* X1;      // GATHER: subtrahend rows (row map i1).  PLAIN: second K segment (or nullptr)
   const int32_t* i0;
   const int32_t* i1;
-  int ld0, ld1, K, KC;
-  const float* Bp;      // packed weights, images of [BN x 128 bytes] per (column tile, K chunk)
+  int ld0, ld1;
+  int K, K2;            // widths of the K segments (K2 == 0: one segment)
+  int KC0, KC;          // chunks of segment 0 / total
+  const float* Bp;      // packed weights, `parts` images of [BN x 128 bytes] per (column tile, K chunk)
   const float* bias;
   float* C;
   int ldc;
   int64_t M;
   int N, BN, n_tiles;
-  float* S;             // optional copy of the operand rows, [M, lds]
+  float* S;             // GATHER: optional copy of the operand rows, [M, lds]
   int lds;
   Dropout drop;         // applied after the activation
   SignBits sign;        // (stored value > 0) bits, written next to C when sign.p != nullptr
-  CUtensorMap mx1;      // X1[M, K] (FLOAT32, box 132 rows x 32 columns, SWIZZLE_128B), used when x1_tma != 0
-  int x1_tma;           // 1: i1(r) == ((r-1)^1)+1 for every r >= 1 (adjacent reverse pairs): X1 rows arrive by TMA
+  int x1_tma;           // GATHER: 1: i1(r) == ((r-1)^1)+1 for every r >= 1 (adjacent reverse pairs): X1 rows arrive by TMA
+  int a_tma;            // PLAIN: 1: rows are 16-byte aligned and arrive by TMA; 0: 4-byte cp.async copies
+  int split;            // 1: 3xTF32 (hi / lo operand images, three MMAs per K step); 0: single-pass TF32
 };
 
 inline int t4_smem_bytes(int BN) {
@@ -74,9 +97,10 @@ inline int t4_smem_bytes(int BN) {
 }
 
 // Epilogue of one accumulator half (128 rows x W columns), 32 columns at a time: the row-owning thread adds its
-// accumulator row to the residual chunk in the (swizzled) ring slot, then the warp writes the 32 rows out with
-// 16-byte stores (8 lanes per row), applying bias + activation.
-template <int ACT>
+// accumulator row to the residual chunk in the (swizzled) ring slot (EPI == E_RES_ACT; otherwise the slot is only the
+// transpose staging of this warp's 32 rows), then the warp writes the 32 rows out with 16-byte stores (8 lanes per
+// row), applying bias + activation.
+template <int EPI, int ACT>
 __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T4Barriers* bar,
                                             uint32_t& rit, int W, int64_t row0, int64_t M, int col0, int N, int cmax,
                                             const float* bias, float* C, int ldc, long long* tacc,
@@ -94,14 +118,18 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
 #pragma unroll
       for (int j = 16; j < 32; ++j) v[j] = 0.f;
     }
-    T2_WAIT(8, &bar->r_full[slot], (rit / T4_R_SLOTS) & 1);
+    if (EPI == E_RES_ACT) T2_WAIT(8, &bar->r_full[slot], (rit / T4_R_SLOTS) & 1);
     ptx::tmem_ld_wait();
     uint8_t* myrow = sl + lane * 128;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float4* q = reinterpret_cast<float4*>(myrow + ((j ^ (lane & 7)) << 4));
-      const float4 r = *q;
-      *q = make_float4(v[4 * j] + r.x, v[4 * j + 1] + r.y, v[4 * j + 2] + r.z, v[4 * j + 3] + r.w);
+      float4 x = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      if (EPI == E_RES_ACT) {
+        const float4 r = *q;
+        x = make_float4(x.x + r.x, x.y + r.y, x.z + r.z, x.w + r.w);
+      }
+      *q = x;
     }
     __syncwarp();
     const int pc = lane & 7, rq = lane >> 3;
@@ -126,15 +154,19 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     // after the stores (as it was) it serialised every 32-column chunk on the store latency (role wait-cycle
     // counters, profiles/r1_k_t4_role_wait_breakdown.log: the epilogue was 77 % busy and the MMA waited 20 % of the
     // kernel for a free accumulator).
-    ptx::fence_proxy_async_smem();            // generic accesses of the slot are ordered before the next TMA write
-    __syncwarp();
-    if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
+    if (EPI == E_RES_ACT) {
+      ptx::fence_proxy_async_smem();          // generic accesses of the slot are ordered before the next TMA write
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
+    } else {
+      __syncwarp();                           // the next chunk's row owners overwrite this warp's staging rows
+    }
     float* cp = C + (row0 + we * 32 + rq) * ldc + colb;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
-      x = f4_act<ACT>(x);
-      if (drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
+      if (EPI != E_STORE) x = f4_act<ACT>(x);
+      if (EPI != E_STORE && drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
       if (in_c && row0 + we * 32 + rq + 4 * i < M) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
       if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
@@ -143,9 +175,11 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
   if (sign.p != nullptr) sign_flush(sign, sw, sign_tile, row0 + we * 32, M, lane >> 3, lane & 7, (W + 31) >> 5);
 }
 
-template <int ACT, bool PREACT>
+template <int AMODE, int EPI, int ACT, bool PREACT>
 __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constant__ T4Params p) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
+  constexpr bool GATHER = AMODE == A_GATHER_DIFF;
+  static_assert(GATHER || !PREACT, "PREACT belongs to the gathered operand");
   extern __shared__ uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = ptx::smem_u32(smem_raw);
@@ -158,17 +192,21 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
   const long long t_start = clock64();
 
   if (threadIdx.x == 0) {
+    // arrivals on raw_full: the 128 loader threads' cp.async groups (+ the expect_tx arrival of the X1 box), or the
+    // single expect_tx arrival of the PLAIN operand's TMA box
+    const uint32_t raw_count = GATHER ? 32 * T4_LOAD_WARPS + (p.x1_tma ? 1 : 0) : (p.a_tma ? 1 : 32 * T4_LOAD_WARPS);
     for (int s = 0; s < T4_A_STAGES; ++s) {
-      ptx::mbar_init(&bar->raw_full[s], 32 * T4_LOAD_WARPS + (p.x1_tma ? 1 : 0));   // + the TMA's expect_tx arrival
+      ptx::mbar_init(&bar->raw_full[s], raw_count);
       ptx::mbar_init(&bar->op_full[s], T4_XFORM_WARPS);
       ptx::mbar_init(&bar->a_empty[s], 1);
     }
-    for (int s = 0; s < T4_B_STAGES; ++s) { ptx::mbar_init(&bar->b_full[s], 1); ptx::mbar_init(&bar->b_empty[s], 1); }
+    for (int s = 0; s < T4_B_SLOTS; ++s) { ptx::mbar_init(&bar->b_full[s], 1); ptx::mbar_init(&bar->b_empty[s], 1); }
     for (int s = 0; s < T4_R_SLOTS; ++s) { ptx::mbar_init(&bar->r_full[s], 1); ptx::mbar_init(&bar->r_empty[s], T2_EPI_WARPS); }
     for (int a = 0; a < 3; ++a) { ptx::mbar_init(&bar->tmem_full[a], 1); ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS); }
     ptx::fence_barrier_init();
-    ptx::tma_prefetch_desc(&p.mr);
-    if (p.x1_tma) ptx::tma_prefetch_desc(&p.mx1);
+    if (EPI == E_RES_ACT) ptx::tma_prefetch_desc(&p.mr);
+    if (GATHER && p.x1_tma) ptx::tma_prefetch_desc(&p.mx1);
+    if (!GATHER && p.a_tma) ptx::tma_prefetch_desc(&p.ma[0]);
   }
   if (warp == T4_MMA_WARP) ptx::tmem_alloc(&bar->tmem_base, TC_TMEM_COLS);
   ptx::tc_fence_before();
@@ -177,9 +215,13 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
   const uint32_t tmem_base = bar->tmem_base;
   const int64_t total = ceil_div(p.M, TC_BM) * p.n_tiles;
   const int W0 = min(p.BN, T4_HALF), W1 = p.BN - W0;                  // accumulator halves of a column tile
+  // The weight ring holds T4_B_STAGES chunk images [BN x 128 bytes]; it is filled and drained in UNITS of one
+  // accumulator half of one image (hi, then lo when split), each unit with its own full / empty barrier: unit u
+  // lives in slot u % (2 nh) = (stage, half).
+  const int nh = W1 > 0 ? 2 : 1, parts = p.split ? 2 : 1, nslots = T4_B_STAGES * nh;
 
   if (warp >= T4_XFORM_W0) {
-    // ================= transform, in place: X0 <- tf32(X0 - act?(X1)) =================
+    // ================= transform, in place: X0 <- tf32(a), X1 part <- tf32(a - tf32(a)),  a = X0 - act?(X1) =================
     // (Fetching the subtrahend rows with plain loads into registers instead was measured SLOWER: the proxy fence
     //  below is a MEMBAR that also waits for the thread's outstanding global loads, i.e. for the prefetch.)
     const int t = threadIdx.x - 32 * T4_XFORM_W0, c = t & 7, rb = t >> 3;
@@ -187,11 +229,11 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
       const int64_t row0 = (tile / p.n_tiles) * TC_BM;
-      const bool keep = p.S != nullptr && (tile % p.n_tiles) == 0;
+      const bool keep = GATHER && p.S != nullptr && (tile % p.n_tiles) == 0;
       uint32_t uoff[T4_XJ];                       // where this thread's subtrahend pieces sit in the X1 part of a stage
 #pragma unroll
       for (int j = 0; j < T4_XJ; ++j) {
-        if (p.x1_tma) {                           // box row of the partner bond: rev(r) - (row0 - T4_X1_LEAD)
+        if (GATHER && p.x1_tma) {                 // box row of the partner bond: rev(r) - (row0 - T4_X1_LEAD)
           const int64_t r = row0 + rb + T4_XR * j;
           const int64_t rv = r >= 1 ? ((r - 1) ^ 1) + 1 : 0;
           const int pr = (int)(rv - row0) + T4_X1_LEAD;            // in [1, 130] by construction
@@ -204,19 +246,31 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         const int s = it % T4_A_STAGES;
         T2_WAIT(0, &bar->raw_full[s], (it / T4_A_STAGES) & 1);
         uint8_t* st = ringA + s * T4_A_STAGE + po;
-        const uint8_t* x1 = ringA + s * T4_A_STAGE + TC_A_STAGE;
+        uint8_t* x1 = ringA + s * T4_A_STAGE + TC_A_STAGE;
         float4 v[T4_XJ], u[T4_XJ];
 #pragma unroll
         for (int j = 0; j < T4_XJ; ++j) {
           v[j] = *reinterpret_cast<const float4*>(st + j * (T4_XR * 128));
-          u[j] = *reinterpret_cast<const float4*>(x1 + uoff[j]);
+          if (GATHER) u[j] = *reinterpret_cast<const float4*>(x1 + uoff[j]);
         }
+        // a_lo goes where the subtrahend rows are: with the shared TMA box another thread's partner row lies under
+        // this thread's a_lo position, so every transform thread must have read its pieces first
+        if (GATHER && p.split && p.x1_tma) ptx::bar_sync(1, 32 * T4_XFORM_WARPS);
 #pragma unroll
         for (int j = 0; j < T4_XJ; ++j) {
-          if (PREACT) u[j] = f4_act<ACT>(u[j]);
-          v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
-          *reinterpret_cast<float4*>(st + j * (T4_XR * 128)) =
-              make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
+          if (GATHER) {
+            if (PREACT) u[j] = f4_act<ACT>(u[j]);
+            v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
+          }
+          const float4 hi = make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
+          *reinterpret_cast<float4*>(st + j * (T4_XR * 128)) = hi;
+          if (p.split) {     // correction image row: 64 bf16 = [a_lo(k = 0..31) | a_hi(k = 0..31)], SWIZZLE_128B
+            uint8_t* row = x1 + (rb + T4_XR * j) * 128 + (c & 1) * 8;
+            *reinterpret_cast<uint2*>(row + (((c >> 1) ^ (rb & 7)) << 4)) =
+                make_uint2(ptx::pack_bf16(v[j].x - hi.x, v[j].y - hi.y), ptx::pack_bf16(v[j].z - hi.z, v[j].w - hi.w));
+            *reinterpret_cast<uint2*>(row + (((4 + (c >> 1)) ^ (rb & 7)) << 4)) =
+                make_uint2(ptx::pack_bf16(hi.x, hi.y), ptx::pack_bf16(hi.z, hi.w));
+          }
         }
         ptx::fence_proxy_async_smem();
         __syncwarp();
@@ -232,65 +286,109 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
       }
     }
   } else if (warp >= T4_LOAD_W0) {
-    // ================= gather loaders: cp.async, 8 threads per row, rows rb + 16 j =================
-    const int t = threadIdx.x - 32 * T4_LOAD_W0, c = t & 7, rb = t >> 3;
+    const int t = threadIdx.x - 32 * T4_LOAD_W0;
     const uint32_t ring_u32 = ptx::smem_u32(ringA);
-    const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));
-    uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
-      const float* s0[8];
-      const float* s1[8];
-      uint32_t okmask = 0;
+    if (GATHER) {
+      // ================= gather loaders: cp.async, 8 threads per row, rows rb + 16 j =================
+      const int c = t & 7, rb = t >> 3;
+      const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+        const float* s0[8];
+        const float* s1[8];
+        uint32_t okmask = 0;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int64_t r = row0 + rb + 16 * j;
-        const bool ok = r < p.M;
-        okmask |= (ok ? 1u : 0u) << j;
-        int64_t a = ok ? r : 0, b = a;
-        if (ok && p.i0) a = __ldg(p.i0 + r);
-        if (ok && p.i1 && !p.x1_tma) b = __ldg(p.i1 + r);
-        s0[j] = p.X0 + a * p.ld0 + c * 4;
-        s1[j] = p.X1 + b * p.ld1 + c * 4;
+        for (int j = 0; j < 8; ++j) {
+          const int64_t r = row0 + rb + 16 * j;
+          const bool ok = r < p.M;
+          okmask |= (ok ? 1u : 0u) << j;
+          int64_t a = ok ? r : 0, b = a;
+          if (ok && p.i0) a = __ldg(p.i0 + r);
+          if (ok && p.i1 && !p.x1_tma) b = __ldg(p.i1 + r);
+          s0[j] = p.X0 + a * p.ld0 + c * 4;
+          s1[j] = p.X1 + b * p.ld1 + c * 4;
+        }
+        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+          const int s = it % T4_A_STAGES;
+          T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+          const int k = kc * TC_BK + c * 4;
+          const int rem = (p.K - k) * 4;
+          const uint32_t valid = rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u);
+          const uint32_t d0 = ring_u32 + s * T4_A_STAGE + po;
+          if (p.x1_tma) {                           // subtrahend rows: one TMA box; minuend rows: gathered cp.async
+            if (t == 0) {
+              ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)(T4_X1_ROWS * 128));
+              ptx::tma_load_2d(ringA + s * T4_A_STAGE + TC_A_STAGE, &p.mx1, kc * TC_BK, (int)row0 - T4_X1_LEAD,
+                               &bar->raw_full[s]);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t v = ((okmask >> j) & 1u) ? valid : 0u;
+              ptx::cp_async16(d0 + j * 2048, v ? s0[j] + kc * TC_BK : p.X0, v);
+            }
+          } else if (okmask == 0xFFu && valid == 16u) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              ptx::cp_async16(d0 + j * 2048, s0[j] + kc * TC_BK, 16u);
+              ptx::cp_async16(d0 + j * 2048 + TC_A_STAGE, s1[j] + kc * TC_BK, 16u);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t v = ((okmask >> j) & 1u) ? valid : 0u;
+              ptx::cp_async16(d0 + j * 2048, v ? s0[j] + kc * TC_BK : p.X0, v);
+              ptx::cp_async16(d0 + j * 2048 + TC_A_STAGE, v ? s1[j] + kc * TC_BK : p.X1, v);
+            }
+          }
+          ptx::cp_async_arrive(&bar->raw_full[s]);
+        }
       }
-      for (int kc = 0; kc < p.KC; ++kc, ++it) {
-        const int s = it % T4_A_STAGES;
-        T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
-        const int k = kc * TC_BK + c * 4;
-        const int rem = (p.K - k) * 4;
-        const uint32_t valid = rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u);
-        const uint32_t d0 = ring_u32 + s * T4_A_STAGE + po;
-        if (p.x1_tma) {                           // subtrahend rows: one TMA box; minuend rows: gathered cp.async
-          if (t == 0) {
-            ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)(T4_X1_ROWS * 128));
-            ptx::tma_load_2d(ringA + s * T4_A_STAGE + TC_A_STAGE, &p.mx1, kc * TC_BK, (int)row0 - T4_X1_LEAD,
+    } else if (p.a_tma) {
+      // ================= plain operand: one TMA box (128 rows x 32 columns, raw fp32) per K chunk =================
+      if (t == 0) {
+        uint32_t it = 0;
+        for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+          const int row0 = (int)((tile / p.n_tiles) * TC_BM);
+          for (int kc = 0; kc < p.KC; ++kc, ++it) {
+            const int s = it % T4_A_STAGES;
+            T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+            const bool second = kc >= p.KC0;
+            ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)TC_A_STAGE);
+            ptx::tma_load_2d(ringA + s * T4_A_STAGE, &p.ma[second ? 1 : 0], (second ? kc - p.KC0 : kc) * TC_BK, row0,
                              &bar->raw_full[s]);
           }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t v = ((okmask >> j) & 1u) ? valid : 0u;
-            ptx::cp_async16(d0 + j * 2048, v ? s0[j] + kc * TC_BK : p.X0, v);
-          }
-        } else if (okmask == 0xFFu && valid == 16u) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            ptx::cp_async16(d0 + j * 2048, s0[j] + kc * TC_BK, 16u);
-            ptx::cp_async16(d0 + j * 2048 + TC_A_STAGE, s1[j] + kc * TC_BK, 16u);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t v = ((okmask >> j) & 1u) ? valid : 0u;
-            ptx::cp_async16(d0 + j * 2048, v ? s0[j] + kc * TC_BK : p.X0, v);
-            ptx::cp_async16(d0 + j * 2048 + TC_A_STAGE, v ? s1[j] + kc * TC_BK : p.X1, v);
-          }
         }
-        ptx::cp_async_arrive(&bar->raw_full[s]);
+      }
+    } else {
+      // ================= plain operand, rows only 4-byte aligned (dense 133 / 147-float feature rows) =================
+      const int col = t & 31, r4 = t >> 5;
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+          const int s = it % T4_A_STAGES;
+          T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+          const bool second = kc >= p.KC0;
+          const float* X = second ? p.X1 : p.X0;
+          const int ld = second ? p.ld1 : p.ld0, Ks = second ? p.K2 : p.K;
+          const int k = (second ? kc - p.KC0 : kc) * TC_BK + col;
+          const bool vk = k < Ks;
+          const uint32_t d0 = ring_u32 + s * T4_A_STAGE + (uint32_t)((col & 3) * 4);
+#pragma unroll 8
+          for (int j = 0; j < TC_BM / T4_LOAD_WARPS; ++j) {
+            const int rl = r4 + T4_LOAD_WARPS * j;
+            const int64_t r = row0 + rl;
+            const uint32_t v = (vk && r < p.M) ? 4u : 0u;
+            ptx::cp_async4(d0 + ptx::sw128_off(rl, col >> 2), v ? X + r * ld + k : X, v);
+          }
+          ptx::cp_async_arrive(&bar->raw_full[s]);
+        }
       }
     }
   } else if (warp == T4_R_WARP) {
     // ================= residual loader: TMA boxes of 128 rows x 32 columns, ahead of the epilogue =================
-    if (lane == 0) {
+    if (EPI == E_RES_ACT && lane == 0) {
       uint32_t rit = 0;
       for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
         const int row0 = (int)((tile / p.n_tiles) * TC_BM);
@@ -305,54 +403,76 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
       }
     }
   } else if (warp == T4_B_WARP) {
-    // ================= weight loader: one bulk copy per K chunk =================
+    // ================= weight loader: one bulk copy per unit (K chunk, hi | lo image, accumulator half) =================
     if (lane == 0) {
-      uint32_t it = 0;
+      uint32_t u = 0;
       for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
         const int nt = (int)(tile % p.n_tiles);
-        for (int kc = 0; kc < p.KC; ++kc, ++it) {
-          const int bs = it % T4_B_STAGES;
-          T2_WAIT(3, &bar->b_empty[bs], ((it / T4_B_STAGES) & 1) ^ 1);
-          ptx::mbar_arrive_expect_tx(&bar->b_full[bs], (uint32_t)b_stage);
-          ptx::bulk_g2s(ringB + bs * b_stage, p.Bp + ((int64_t)nt * p.KC + kc) * p.BN * 32, (uint32_t)b_stage, &bar->b_full[bs]);
+        for (int kc = 0; kc < p.KC; ++kc) {
+          for (int part = 0; part < parts; ++part) {
+            const float* img = p.Bp + (((int64_t)nt * p.KC + kc) * parts + part) * p.BN * 32;
+            for (int hb = 0; hb < nh; ++hb, ++u) {
+              const int slot = u % nslots;
+              T2_WAIT(3, &bar->b_empty[slot], ((u / nslots) & 1) ^ 1);
+              const uint32_t bytes = (uint32_t)((hb ? W1 : W0) * 128);
+              ptx::mbar_arrive_expect_tx(&bar->b_full[slot], bytes);
+              ptx::bulk_g2s(ringB + (slot / nh) * b_stage + (hb ? W0 * 128 : 0), img + (hb ? W0 * 32 : 0), bytes,
+                            &bar->b_full[slot]);
+            }
+          }
         }
       }
     }
   } else if (warp == T4_MMA_WARP) {
     // ================= MMA issue: two accumulator halves per tile, three rotating TMEM buffers =================
-    uint32_t it = 0, g = 0;                                              // g: accumulator halves issued so far
-    const uint32_t id0 = ptx::idesc_tf32(128, W0), id1 = ptx::idesc_tf32(128, W1 > 0 ? W1 : 16);
+    uint32_t it = 0, g = 0, u = 0;                                      // g: accumulator halves issued so far; u: weight units
+    const uint32_t idh[2] = {ptx::idesc_tf32(128, W0), ptx::idesc_tf32(128, W1 > 0 ? W1 : 16)};
+    const uint32_t idc[2] = {ptx::idesc_bf16(128, W0), ptx::idesc_bf16(128, W1 > 0 ? W1 : 16)};
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      const uint32_t g0 = g, g1 = g + 1;
-      g += W1 > 0 ? 2 : 1;
+      const uint32_t g0 = g;
+      g += nh;
       for (int kc = 0; kc < p.KC; ++kc, ++it) {
-        const int s = it % T4_A_STAGES, bs = it % T4_B_STAGES;
+        const int s = it % T4_A_STAGES;
         T2_WAIT(5, &bar->op_full[s], (it / T4_A_STAGES) & 1);
-        T2_WAIT(6, &bar->b_full[bs], (it / T4_B_STAGES) & 1);
-        const uint32_t a_addr = ptx::smem_u32(ringA + s * T4_A_STAGE), b_addr = ptx::smem_u32(ringB + bs * b_stage);
-        if (kc == 0) T2_WAIT(4, &bar->tmem_empty[g0 % 3], ((g0 / 3) & 1) ^ 1);
-        ptx::tc_fence_after();
-        if (lane == 0) {
-#pragma unroll
-          for (int ks = 0; ks < 4; ++ks)
-            ptx::mma_tf32(tmem_base + (g0 % 3) * T4_HALF, ptx::smem_desc_sw128(a_addr + ks * 32),
-                          ptx::smem_desc_sw128(b_addr + ks * 32), id0, (kc == 0 && ks == 0) ? 0u : 1u);
-        }
-        if (W1 > 0) {
-          if (kc == 0) { T2_WAIT(4, &bar->tmem_empty[g1 % 3], ((g1 / 3) & 1) ^ 1); ptx::tc_fence_after(); }
-          if (lane == 0) {
-#pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-              ptx::mma_tf32(tmem_base + (g1 % 3) * T4_HALF, ptx::smem_desc_sw128(a_addr + ks * 32),
-                            ptx::smem_desc_sw128(b_addr + W0 * 128 + ks * 32), id1, (kc == 0 && ks == 0) ? 0u : 1u);
+        const uint32_t a_hi = ptx::smem_u32(ringA + s * T4_A_STAGE), a_lo = a_hi + TC_A_STAGE;
+        // Issue order: consecutive MMAs alternate between the two accumulator halves (independent chains; measured
+        // 3 % faster than half by half).  part 0: a_hi w_hi in kind::tf32.  part 1 (3xTF32): ONE kind::f16 (bf16)
+        // group over the correction images, K = 64 per chunk: [bf16 a_lo | bf16 a_hi] . [bf16 w_hi | bf16 w_lo].
+        for (int part = 0; part < parts; ++part) {
+          uint32_t b_addr[2] = {0u, 0u}, d[2] = {0u, 0u};
+          int slots[2] = {0, 0};
+          for (int hb = 0; hb < nh; ++hb, ++u) {
+            const int slot = u % nslots;
+            slots[hb] = slot;
+            T2_WAIT(6, &bar->b_full[slot], (u / nslots) & 1);
+            const uint32_t gb = g0 + hb;
+            if (kc == 0 && part == 0) T2_WAIT(4, &bar->tmem_empty[gb % 3], ((gb / 3) & 1) ^ 1);
+            b_addr[hb] = ptx::smem_u32(ringB + (slot / nh) * b_stage + (hb ? W0 * 128 : 0));
+            d[hb] = tmem_base + (gb % 3) * T4_HALF;
           }
+          ptx::tc_fence_after();
+          if (lane == 0) {
+            if (part == 0) {
+#pragma unroll
+              for (int ks = 0; ks < 4; ++ks)
+                for (int hb = 0; hb < nh; ++hb)
+                  ptx::mma_tf32(d[hb], ptx::smem_desc_sw128(a_hi + ks * 32), ptx::smem_desc_sw128(b_addr[hb] + ks * 32), idh[hb],
+                                (kc == 0 && ks == 0) ? 0u : 1u);
+            } else {
+#pragma unroll
+              for (int ks = 0; ks < 4; ++ks)
+                for (int hb = 0; hb < nh; ++hb)
+                  ptx::mma_bf16(d[hb], ptx::smem_desc_sw128(a_lo + ks * 32), ptx::smem_desc_sw128(b_addr[hb] + ks * 32), idc[hb], 1u);
+            }
+            for (int hb = 0; hb < nh; ++hb) ptx::tc_commit(&bar->b_empty[slots[hb]]);
+          }
+          __syncwarp();
         }
         if (lane == 0) {
           ptx::tc_commit(&bar->a_empty[s]);
-          ptx::tc_commit(&bar->b_empty[bs]);
           if (kc == p.KC - 1) {
             ptx::tc_commit(&bar->tmem_full[g0 % 3]);
-            if (W1 > 0) ptx::tc_commit(&bar->tmem_full[g1 % 3]);
+            if (nh > 1) ptx::tc_commit(&bar->tmem_full[(g0 + 1) % 3]);
           }
         }
         __syncwarp();
@@ -364,13 +484,13 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
       const int64_t row0 = (tile / p.n_tiles) * TC_BM;
       const int col0 = (int)(tile % p.n_tiles) * p.BN;
-      for (int hb = 0; hb < (W1 > 0 ? 2 : 1); ++hb, ++g) {
+      for (int hb = 0; hb < nh; ++hb, ++g) {
         const int buf = g % 3;
         T2_WAIT(7, &bar->tmem_full[buf], (g / 3) & 1);
         ptx::tc_fence_after();
-        t4_epilogue<ACT>(tmem_base + buf * T4_HALF, warp, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
-                         col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop, p.sign,
-                         (int)(tile % p.n_tiles) * p.sign.tpn + hb);
+        t4_epilogue<EPI, ACT>(tmem_base + buf * T4_HALF, warp, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
+                              col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop, p.sign,
+                              (int)(tile % p.n_tiles) * p.sign.tpn + hb);
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[buf]);

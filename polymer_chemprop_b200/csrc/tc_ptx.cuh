@@ -64,6 +64,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// named barrier over `nthreads` threads (a multiple of 32) of the CTA; id 0 is __syncthreads()
+__device__ __forceinline__ void bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // generic-proxy smem writes -> visible to the async proxy (tcgen05.mma / bulk copies)
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -122,6 +127,16 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// same with bf16 inputs (kind::f16, K = 16 per instruction): the correction terms of the 3xTF32 scheme
+__device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // 32 lanes x 32 columns of fp32: thread i of the warp gets TMEM lane (base_lane + i), 32 columns.
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   uint32_t* u = reinterpret_cast<uint32_t*>(v);
@@ -155,6 +170,13 @@ __device__ __forceinline__ float to_tf32(float x) {  // round-to-nearest (the MM
   return __uint_as_float(r);
 }
 
+// two fp32 -> packed bf16x2 (round to nearest even); `lo` lands in the lower 16 bits = the lower address
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 // ---- descriptors ---------------------------------------------------------------------------
 // Shared-memory matrix descriptor, K-major operand, SWIZZLE_128B: rows of 128 bytes (32 tf32),
 // 8-row groups 1024 bytes apart (SBO), tile base 1024-byte aligned.  Fields (cute
@@ -175,6 +197,11 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr) {
 // [17,23) N>>3, [24,29) M>>4.
 __host__ __device__ inline uint32_t idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// kind::f16 with bf16 inputs: a_format = b_format = 1 (BF16), fp32 accumulate
+__host__ __device__ inline uint32_t idesc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // byte offset of 16-byte chunk `c` (0..7) of row `r` inside a SWIZZLE_128B K-major tile

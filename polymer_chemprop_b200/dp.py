@@ -30,9 +30,14 @@ def shard_graphs(graphs: Sequence, rank: int, world: int) -> List:
 
 
 class FlatGradAllReduce:
-    """Packs the ``.grad`` of ``params`` into one flat fp32 buffer, all-reduces it once and scatters the
-    (averaged) result back into the ``.grad`` tensors.  Parameters without a gradient contribute zeros
-    (every rank must issue the same collective)."""
+    """One flat fp32 buffer for the gradients of ``params``, all-reduced with ONE collective per step.
+
+    ``attach(model)``: every ``MPNEncoder`` of ``model`` whose parameters are all in ``params`` writes its weight
+    gradients STRAIGHT into this buffer (``wd_encoder_backward`` takes plain pointers: ``WdGrads`` are views of
+    ``flat``) and each such parameter's ``.grad`` IS its view, so nothing is packed or unpacked around the
+    collective: per step the data-parallel path costs exactly one ``ncclAllReduce(avg)``.  Parameters outside an
+    attached encoder (an FFN head, say) are packed / unpacked with one fused copy each way.  Parameters without a
+    gradient contribute zeros (every rank must issue the same collective)."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], group: Optional[dist.ProcessGroup] = None,
                  average: bool = True):
@@ -47,25 +52,72 @@ class FlatGradAllReduce:
             raise ValueError("all parameters must share one device and dtype")
         self.flat = torch.zeros(sum(self.sizes), device=dev, dtype=dt)
         self.views = list(self.flat.split(self.sizes))
+        self._view_of = {id(p): v.view_as(p) for p, v in zip(self.params, self.views)}
+        self._attached = {}         # id(encoder) -> (encoder, [views in WdGrads order], [params])
+        self._written = set()       # encoders whose backward has written this step's gradients into the buffer
 
     @property
     def nbytes(self) -> int:
         return self.flat.numel() * self.flat.element_size()
 
+    # ---- gradient sink of the encoders (polymer_chemprop_b200.mpn._EncoderFunction.backward) -----------------
+    def attach(self, model: torch.nn.Module) -> int:
+        """Makes this buffer the gradient sink of the MPNEncoders in ``model``; returns how many were attached."""
+        from .mpn import MPNEncoder
+        n = 0
+        for enc in {id(m): m for m in model.modules() if isinstance(m, MPNEncoder)}.values():
+            ps = (enc.W_i.weight, enc.W_i.bias, enc.W_h.weight, enc.W_h.bias, enc.W_o.weight, enc.W_o.bias)
+            if any(p is not None and id(p) not in self._view_of for p in ps):
+                continue
+            self._attached[id(enc)] = (enc, [self._view_of[id(p)] if p is not None else None for p in ps], ps)
+            enc._grad_sink = self
+            n += 1
+        return n
+
+    def detach(self):
+        for enc, _v, _p in self._attached.values():
+            enc._grad_sink = None
+        self._attached.clear()
+
+    def take(self, enc) -> bool:
+        """True: the calling backward may OVERWRITE the encoder's slices (its first backward since the last
+        all-reduce); False: a second application of a shared encoder -- it must go through autograd's accumulation."""
+        if id(enc) not in self._attached or id(enc) in self._written:
+            return False
+        _e, views, ps = self._attached[id(enc)]
+        if any(p is not None and p.grad is not None and p.grad.data_ptr() != v.data_ptr() for p, v in zip(ps, views)):
+            return False                                    # someone else has already accumulated into a separate .grad
+        self._written.add(id(enc))
+        for p, v in zip(ps, views):
+            if p is not None:
+                p.grad = v
+        return True
+
+    def views_for(self, enc):
+        return self._attached[id(enc)][1]
+
     def __call__(self) -> torch.Tensor:
         world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        src, dst = [], []
         for p, v in zip(self.params, self.views):
             if p.grad is None:
                 v.zero_()
-            else:
-                v.copy_(p.grad.reshape(-1))
+            elif p.grad.data_ptr() != v.data_ptr():
+                src.append(p.grad.reshape(-1))
+                dst.append(v)
+        if src:
+            torch._foreach_copy_(dst, src)                  # one fused launch for everything outside the sinks
         if world > 1:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
-            if self.average:
-                self.flat.div_(world)
-        for p, v in zip(self.params, self.views):
-            if p.grad is None:
-                p.grad = v.view_as(p).clone()
+            backend = dist.get_backend(self.group)
+            if self.average and backend == "nccl":          # ncclAvg: the 1/R scale rides inside the collective
+                dist.all_reduce(self.flat, op=dist.ReduceOp.AVG, group=self.group)
             else:
-                p.grad.copy_(v.view_as(p))
+                dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+                if self.average:
+                    self.flat.div_(world)
+        for p in self.params:                               # every .grad is now its view of the reduced buffer
+            v = self._view_of[id(p)]
+            if p.grad is None or p.grad.data_ptr() != v.data_ptr():
+                p.grad = v
+        self._written.clear()
         return self.flat

@@ -7,6 +7,7 @@ reference, so ``MoleculeModel`` (chemprop/models/model.py:41-47) and existing ch
 kernels through the C ABI; there is no CPU / eager fallback.
 """
 import ctypes as C
+import os
 from functools import reduce
 from typing import List, Optional
 
@@ -39,11 +40,12 @@ class DeviceGraph:
         """``stream``: build on that CUDA stream without blocking the host (pinned host tensors are
         copied with non_blocking=True); consumers wait on ``self.ready``.  Validation of the graph
         invariants is deferred to ``check()`` (first use), which only waits for this graph's own work."""
-        if stream is not None:
-            with torch.cuda.stream(stream):
-                self._build(mol_graph, device, non_blocking=True)
-        else:
-            self._build(mol_graph, device, non_blocking=False)
+        with torch.cuda.device(device):     # the library launches on the current device (the reference never sets it)
+            if stream is not None:
+                with torch.cuda.stream(stream):
+                    self._build(mol_graph, device, non_blocking=True)
+            else:
+                self._build(mol_graph, device, non_blocking=False)
         self._validate = validate
         self._checked = False
 
@@ -200,17 +202,22 @@ class _EncoderFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, enc, dg, cfg, W_i, b_i, W_h, b_h, W_o, b_o):
         dev = dg.device
-        ws_bytes = _capi.lib().wd_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
-        if ws_bytes == 0:
-            _capi.check(_capi.WD_ERR_INVALID_ARG)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        out = torch.empty((dg.n_mols, enc.hidden_size), dtype=torch.float32, device=dev)
-        ws_c = [t.detach().contiguous() if t is not None else None for t in (W_i, b_i, W_h, b_h, W_o, b_o)]
-        weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
-        _capi.check(_capi.lib().wd_encoder_forward(C.byref(dg.struct), C.byref(weights), C.byref(cfg),
-                                                   _capi.ptr(ws), ws_bytes, _capi.ptr(out),
-                                                   _capi.current_stream(dev)))
-        ctx.enc, ctx.dg, ctx.cfg, ctx.ws, ctx.ws_bytes, ctx.weights_c = enc, dg, cfg, ws, ws_bytes, ws_c
+        with torch.cuda.device(dev):        # the library launches on the CURRENT device: the reference never calls set_device
+            ws_bytes = _capi.lib().wd_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
+            if ws_bytes == 0:
+                _capi.check(_capi.WD_ERR_INVALID_ARG)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            out = torch.empty((dg.n_mols, enc.hidden_size), dtype=torch.float32, device=dev)
+            ws_c = [t.detach().contiguous() if t is not None else None for t in (W_i, b_i, W_h, b_h, W_o, b_o)]
+            weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
+            _capi.check(_capi.lib().wd_encoder_forward(C.byref(dg.struct), C.byref(weights), C.byref(cfg),
+                                                       _capi.ptr(ws), ws_bytes, _capi.ptr(out),
+                                                       _capi.current_stream(dev)))
+        # the parameters themselves are saved (not detached aliases): autograd's version counters then catch an
+        # in-place update (an optimizer step) between this forward and its backward
+        ctx.present = [t is not None for t in (W_i, b_i, W_h, b_h, W_o, b_o)]
+        ctx.save_for_backward(*[t for t in (W_i, b_i, W_h, b_h, W_o, b_o) if t is not None])
+        ctx.enc, ctx.dg, ctx.cfg, ctx.ws, ctx.ws_bytes = enc, dg, cfg, ws, ws_bytes
         ctx.has_bias = b_i is not None
         return out
 
@@ -218,19 +225,35 @@ class _EncoderFunction(torch.autograd.Function):
     def backward(ctx, d_out):
         enc, dg, cfg = ctx.enc, ctx.dg, ctx.cfg
         dev = dg.device
-        W_i, b_i, W_h, b_h, W_o, b_o = ctx.weights_c
-        d_out = d_out.contiguous().float()
-        gW_i, gW_h, gW_o, gb_o = (torch.empty_like(t) for t in (W_i, W_h, W_o, b_o))
-        gb_i = torch.empty_like(b_i) if ctx.has_bias else None
-        gb_h = torch.empty_like(b_h) if ctx.has_bias else None
-        weights = _capi.WdWeights(*[_capi.ptr(t) for t in ctx.weights_c])
-        grads = _capi.WdGrads(*[_capi.ptr(t) for t in (gW_i, gb_i, gW_h, gb_h, gW_o, gb_o)])
-        _capi.check(_capi.lib().wd_encoder_backward(C.byref(dg.struct), C.byref(weights), C.byref(cfg),
-                                                    _capi.ptr(ctx.ws), ctx.ws_bytes, _capi.ptr(d_out),
-                                                    C.byref(grads), _capi.current_stream(dev)))
+        if ctx.ws is None:
+            raise RuntimeError("the B200 encoder's backward ran twice on one forward: the workspace holding the saved "
+                               "activations is released after the first backward (retain_graph is not supported)")
+        saved = iter(ctx.saved_tensors)                     # raises if a parameter was modified in place since forward
+        W_i, b_i, W_h, b_h, W_o, b_o = [next(saved).detach().contiguous() if here else None for here in ctx.present]
+        sink = enc._grad_sink
+        with torch.cuda.device(dev):
+            d_out = d_out.contiguous().float()
+            direct = sink is not None and sink.take(enc)    # first backward of this encoder in the step: write in place
+            if direct:
+                gW_i, gb_i, gW_h, gb_h, gW_o, gb_o = sink.views_for(enc)
+            else:
+                gW_i, gW_h, gW_o, gb_o = (torch.empty_like(t) for t in (W_i, W_h, W_o, b_o))
+                gb_i = torch.empty_like(b_i) if ctx.has_bias else None
+                gb_h = torch.empty_like(b_h) if ctx.has_bias else None
+            weights = _capi.WdWeights(*[_capi.ptr(t) for t in (W_i, b_i, W_h, b_h, W_o, b_o)])
+            grads = _capi.WdGrads(*[_capi.ptr(t) for t in (gW_i, gb_i, gW_h, gb_h, gW_o, gb_o)])
+            _capi.check(_capi.lib().wd_encoder_backward(C.byref(dg.struct), C.byref(weights), C.byref(cfg),
+                                                        _capi.ptr(ctx.ws), ctx.ws_bytes, _capi.ptr(d_out),
+                                                        C.byref(grads), _capi.current_stream(dev)))
         ctx.ws = None
         if enc.depth == 1:          # W_h is unused by the reference's graph when depth == 1
+            if direct:
+                gW_h.zero_()
+                if gb_h is not None:
+                    gb_h.zero_()
             gW_h, gb_h = None, None
+        if direct:                  # the gradients already sit in the flat buffer and are the parameters' .grad
+            return (None,) * 9
         return None, None, None, gW_i, gb_i, gW_h, gb_h, gW_o, gb_o
 
 
@@ -252,6 +275,7 @@ class MPNEncoder(nn.Module):
         self.aggregation = args.aggregation
         self.aggregation_norm = args.aggregation_norm
         self.math_mode = getattr(args, "wd_math_mode", None) or _default_math_mode()
+        self._grad_sink = None      # dp.FlatGradAllReduce.attach(): the backward writes into the flat gradient buffer
         if self.atom_messages:
             raise NotImplementedError("atom_messages=True is not accelerated by the B200 encoder; "
                                       "use chemprop.models.mpn.MPNEncoder for that mode")
@@ -281,25 +305,31 @@ class MPNEncoder(nn.Module):
         if self.training and self.dropout > 0.0:
             p = float(self.dropout)
             lo, hi = (int(x) & 0xFFFFFFFF for x in torch.randint(0, 2 ** 32, (2,), dtype=torch.int64).tolist())
+        flags = 0
+        if os.environ.get("WD_SIGN_BITS", "1") == "0":      # A/B switch; part of the config: forward and backward agree
+            flags |= _capi.FLAG_NO_SIGN_BITS
+        if os.environ.get("WD_GRAPH", "1") == "0":
+            flags |= _capi.FLAG_NO_GRAPH
         return _capi.WdConfig(self.hidden_size, dg.atom_fdim, dg.bond_fdim, self.depth,
                               _capi.ACTIVATIONS[self.activation], _capi.AGGREGATIONS[self.aggregation],
                               int(bool(self.undirected)), int(bool(self.bias)),
-                              _capi.MATH_MODES[self.math_mode], float(self.aggregation_norm), p, lo, hi)
+                              _capi.MATH_MODES[self.math_mode], float(self.aggregation_norm), p, lo, hi, flags)
 
     def _infer(self, dg: DeviceGraph, cfg: _capi.WdConfig) -> torch.Tensor:
         """Forward only (torch.no_grad(): chemprop/train/predict.py:10-68, molecule_fingerprint.py:151-183):
         wd_encoder_infer keeps nothing for a backward pass, so the workspace is a third of the training one."""
         L, dev = _capi.lib(), dg.device
-        ws_bytes = L.wd_infer_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
-        if ws_bytes == 0:
-            _capi.check(_capi.WD_ERR_INVALID_ARG)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        out = torch.empty((dg.n_mols, self.hidden_size), dtype=torch.float32, device=dev)
-        ws_c = [t.detach().contiguous() if t is not None else None
-                for t in (self.W_i.weight, self.W_i.bias, self.W_h.weight, self.W_h.bias, self.W_o.weight, self.W_o.bias)]
-        weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
-        _capi.check(L.wd_encoder_infer(C.byref(dg.struct), C.byref(weights), C.byref(cfg), _capi.ptr(ws), ws_bytes,
-                                       _capi.ptr(out), _capi.current_stream(dev)))
+        with torch.cuda.device(dev):
+            ws_bytes = L.wd_infer_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
+            if ws_bytes == 0:
+                _capi.check(_capi.WD_ERR_INVALID_ARG)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            out = torch.empty((dg.n_mols, self.hidden_size), dtype=torch.float32, device=dev)
+            ws_c = [t.detach().contiguous() if t is not None else None
+                    for t in (self.W_i.weight, self.W_i.bias, self.W_h.weight, self.W_h.bias, self.W_o.weight, self.W_o.bias)]
+            weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
+            _capi.check(L.wd_encoder_infer(C.byref(dg.struct), C.byref(weights), C.byref(cfg), _capi.ptr(ws), ws_bytes,
+                                           _capi.ptr(out), _capi.current_stream(dev)))
         return out
 
     def forward(self, mol_graph, atom_descriptors_batch: List[np.ndarray] = None) -> torch.Tensor:
@@ -325,8 +355,10 @@ class MPNEncoder(nn.Module):
 
 
 def _default_math_mode() -> str:
-    import os
-    return os.environ.get("WDMPNN_MATH", "fp32")
+    """tf32x3: tcgen05 tensor cores with error-compensated (3xTF32) forward contractions -- fp32-grade encoder output
+    and predictions (<= 1e-4, the bound BASELINE.json states for a tensor-core path) at tensor-core speed.
+    WDMPNN_MATH=tf32 (single pass, ~5e-4 on predictions) or fp32 (CUDA cores) select the other modes."""
+    return os.environ.get("WDMPNN_MATH", "tf32x3")
 
 
 class MPN(nn.Module):

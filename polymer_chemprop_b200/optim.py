@@ -76,18 +76,23 @@ class FlatAdam(torch.optim.Optimizer):
             self.state[p] = {"step": torch.tensor(0.0), "exp_avg": m.view(p.shape), "exp_avg_sq": v.view(p.shape)}
 
     def _pack_grads(self):
+        """Returns the parameters WITHOUT a gradient this step.  torch's Adam skips those entirely (no weight decay, no
+        moment decay, no update: e.g. W_h of a depth-1 encoder, which the reference's graph never touches), so their
+        slices of the parameter and moment buffers are saved here and put back after the fused step."""
+        skipped = [i for i, p in enumerate(self._params) if p.grad is None]
         if self._grad_buffer is not None:
-            return                                          # FlatGradAllReduce.__call__ has filled (and reduced) it
+            return skipped                                  # FlatGradAllReduce.__call__ has filled (and reduced) it
         src, dst = [], []
         for p, v in zip(self._params, self._grad_views):
             if p.grad is None:
-                v.zero_()                                   # torch's Adam skips such parameters; a zero gradient
-            elif p.grad.data_ptr() != v.data_ptr():         # still decays their moments -- documented difference
+                v.zero_()
+            elif p.grad.data_ptr() != v.data_ptr():
                 src.append(p.grad.reshape(-1))
                 dst.append(v)
                 p.grad = v.view(p.shape)                    # zero_grad(set_to_none=False) keeps the flat views alive
         if src:
             torch._foreach_copy_(dst, src)                  # one fused launch for all parameters
+        return skipped
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -95,16 +100,27 @@ class FlatAdam(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        self._pack_grads()
+        skipped = self._pack_grads()
+        keep = []
+        if skipped:                                         # rare (frozen-by-absence parameters): save, step, restore
+            offs = np.concatenate([[0], np.cumsum(self._sizes)])
+            for i in skipped:
+                sl = slice(int(offs[i]), int(offs[i + 1]))
+                keep.append((sl, self.flat_params[sl].clone(), self.exp_avg[sl].clone(), self.exp_avg_sq[sl].clone()))
         g = self.param_groups[0]
         self.steps += 1
         cfg = _capi.WdAdam(float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
                            float(g["weight_decay"]), float(self.max_grad_norm) if self.max_grad_norm else 0.0,
                            self.steps, int(self.decoupled))
         p = _capi.ptr
-        _capi.check(_capi.lib().wd_adam_step(p(self.flat_params), p(self.flat_grads), p(self.exp_avg), p(self.exp_avg_sq),
-                                             self.flat_params.numel(), C.byref(cfg), p(self._scratch), p(self.grad_norm),
-                                             _capi.current_stream(self.flat_params.device)))
+        with torch.cuda.device(self.flat_params.device):    # the library launches on the current device
+            _capi.check(_capi.lib().wd_adam_step(p(self.flat_params), p(self.flat_grads), p(self.exp_avg), p(self.exp_avg_sq),
+                                                 self.flat_params.numel(), C.byref(cfg), p(self._scratch), p(self.grad_norm),
+                                                 _capi.current_stream(self.flat_params.device)))
+        for sl, pv, m, v in keep:
+            self.flat_params[sl].copy_(pv)
+            self.exp_avg[sl].copy_(m)
+            self.exp_avg_sq[sl].copy_(v)
         return loss
 
     def state_dict(self):

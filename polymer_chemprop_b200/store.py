@@ -152,11 +152,12 @@ class DeviceGraphStore:
         idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int64).reshape(-1))
         if idx.size == 0 or idx.min() < 0 or idx.max() >= len(self.graphs):
             raise ValueError("indices out of range or empty")
-        if stream is not None:
-            with torch.cuda.stream(stream):
+        with torch.cuda.device(self.device):    # the library launches on the current device
+            if stream is not None:
+                with torch.cuda.stream(stream):
+                    dg = self._assemble(idx)
+            else:
                 dg = self._assemble(idx)
-        else:
-            dg = self._assemble(idx)
         return StoreBatch(self, idx, dg)
 
     def _assemble(self, idx: np.ndarray) -> DeviceGraph:
