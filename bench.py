@@ -90,13 +90,15 @@ def world_size():
 # --------------------------------------------------------------------------------------------
 # CPU baseline: the oracle port of the reference's op sequence on the host cores
 # --------------------------------------------------------------------------------------------
-def cpu_baseline(graphs, a, budget_s=12.0, max_steps=10, warmup=1):
+def cpu_port_time(graphs, a, n, threads, steps, warmup, readout=True, budget_s=60.0):
+    """Times `steps` forward + backward passes (after `warmup`) of the reference's op sequence (oracle/mpn_oracle.py,
+    torch CPU fp32) on the first n graphs with `threads` torch threads.  Stops early once budget_s is spent (the
+    steps actually timed are reported)."""
     from oracle import mpn_oracle
     from polymer_chemprop_b200 import BatchMolGraph
-    n = min(a.cpu_sample, len(graphs))
+    n = min(n, len(graphs))
     bmg = BatchMolGraph(graphs[:n])
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+    torch.set_num_threads(threads)
     h, fa, fb = a.hidden, bmg.atom_fdim, bmg.bond_fdim
     gen = torch.Generator().manual_seed(0)
     weights = {"W_i.weight": torch.randn(h, fb, generator=gen) * 0.07,
@@ -105,38 +107,73 @@ def cpu_baseline(graphs, a, budget_s=12.0, max_steps=10, warmup=1):
                "W_o.bias": torch.zeros(h)}
     d_out = torch.randn(n, h, generator=gen)
     comps = bmg.get_components()
-    times = []
-    for i in range(warmup + max_steps):
+    times, t_begin = [], time.perf_counter()
+    for i in range(warmup + steps):
         t0 = time.perf_counter()
-        mpn_oracle.encoder_forward_backward(comps, weights, d_out, depth=a.depth)
+        mpn_oracle.encoder_forward_backward(comps, weights, d_out, depth=a.depth, readout=readout)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
-            if sum(times) > budget_s:
-                break
+        if time.perf_counter() - t_begin > budget_s and times:
+            break
     ms = 1e3 * float(np.mean(times))
-    return {"value": n / (ms * 1e-3), "unit": UNIT, "cores": cores, "kind": "port",
-            "threads": torch.get_num_threads(), "ms_per_step": ms, "steps": len(times),
-            "sample": f"first {n} graphs of the rank-0 batch per step, reference op sequence "
-                      f"(oracle/mpn_oracle.py) on torch CPU fp32; cost is super-linear in batch "
-                      f"(per-molecule readout backward), so larger batches are slower per graph"}
+    return {"value": n / (ms * 1e-3), "unit": UNIT, "graphs": n, "threads": torch.get_num_threads(), "ms_per_step": ms,
+            "steps": len(times), "warmup": warmup, "readout": readout}
+
+
+def cpu_baseline(graphs, a, steps=10, warmup=2, extras=True, full_batch=False):
+    """The reference's CPU implementation of the path on the box's host cores (the oracle PORT: the reference is pure
+    Python and /root/reference is not on the GPU box).  Headline = all cores on a CPU_SAMPLE-graph sample of the same
+    workload, the most CPU-favourable batch size (the reference's per-molecule readout backward is super-linear in the
+    batch: 43 graphs/s at B=4096 in the survey container).  extras: the other figures BASELINE.md section 3 promises --
+    batch 50, one thread, message passing only (readout excluded) -- and, for --impl reference, one step at the full
+    labelled batch."""
+    cores = os.cpu_count() or 1
+    n = min(a.cpu_sample, len(graphs))
+    head = cpu_port_time(graphs, a, n, cores, steps, warmup, budget_s=120.0)
+    out = {"value": head["value"], "unit": UNIT, "cores": cores, "kind": "port", "threads": head["threads"],
+           "ms_per_step": head["ms_per_step"], "steps": head["steps"], "warmup": head["warmup"],
+           "sample": f"first {n} graphs of the rank-0 batch per step (forward + backward), reference op sequence "
+                     f"(oracle/mpn_oracle.py) on torch CPU fp32, {cores} threads; the cost per graph grows with the batch "
+                     f"(per-molecule readout backward), so this sample size FAVOURS the CPU against the full batch"}
+    if extras:
+        ex = {}
+        ex["batch_50_all_cores"] = cpu_port_time(graphs, a, 50, cores, 10, 2, budget_s=10.0)
+        ex["one_thread"] = cpu_port_time(graphs, a, n, 1, 2, 1, budget_s=30.0)
+        ex["message_passing_only_all_cores"] = cpu_port_time(graphs, a, n, cores, 5, 1, readout=False, budget_s=15.0)
+        if full_batch and len(graphs) > n:
+            ex["full_batch_all_cores"] = cpu_port_time(graphs, a, len(graphs), cores, 1, 0, budget_s=1.0)
+        out["other_figures"] = ex
+    torch.set_num_threads(cores)
+    return out
+
+
+def base_config(a, world, G, Na, Nb):
+    """The workload description shared by both arms (the driver compares the arms' `config`)."""
+    return {"workload": workload_name(a), "global_batch": world * G, "n_atoms": Na, "n_bonds": Nb,
+            "parallelism": f"dp{world}" if world > 1 else "single GPU",
+            "l2": "per-step working set (workspace >= 2 GB at batch 4096) exceeds the 126 MB L2"}
 
 
 def run_reference(a):
-    """--impl reference: the reference's own CPU implementation of the path.  /root/reference is not on
-    the GPU box and it is pure Python, so the timed code is the oracle port of its op sequence."""
+    """--impl reference: the reference's own CPU implementation of the path, on the arm's config / metric / unit.
+    /root/reference is not on the GPU box and it is pure Python, so the timed code is the oracle port of its op
+    sequence; each of the K steps (after W warm-ups, as asked) is a bounded sample of the workload -- see
+    cpu_baseline()."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from polymer_chemprop_b200 import synth
-    graphs = synth.make_graphs(a.kind, a.cpu_sample, seed=0)
-    steps = max(1, a.steps)
-    cb = cpu_baseline(graphs, a, budget_s=150.0, max_steps=steps, warmup=max(1, min(a.warmup, 2)))
+    from polymer_chemprop_b200 import BatchMolGraph, synth
+    graphs = synth.make_graphs(a.kind, a.batch, seed=0)
+    bmg = BatchMolGraph(graphs)
+    warmup = max(a.warmup, 3)
+    cb = cpu_baseline(graphs, a, steps=max(1, a.steps), warmup=warmup, extras=True,
+                      full_batch=os.environ.get("WD_REF_FULL", "1") != "0")
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
-            "steps": cb["steps"], "warmup": max(1, min(a.warmup, 2)), "ms_per_step": cb["ms_per_step"],
+            "steps": cb["steps"], "warmup": warmup, "ms_per_step": cb["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": workload_name(a), "parallelism": "host cores only"},
-            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "data": "synthetic", "config": base_config(a, max(1, a.gpus), len(graphs), bmg.n_atoms, bmg.n_bonds),
+            "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -234,6 +271,47 @@ def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d, sign_bits=False):
         "misc": 0.0,
         "reduce": 0.0,
     }
+
+
+def contract_bytes(Na, Nb, G, h, Fa, Fb, d):
+    """SURVEY.md section 8(d) "Algorithmic bytes": compulsory traffic as the scope contract counts it (fp32 storage),
+    independent of how this implementation splits the work into kernels.  P = one [N_b, h] pass.
+    Depth step (fused aggregate + gather + W_h + residual + ReLU): 3P (2P for t = 1) + 16 N_b + 4 N_a + 4 h^2;
+    whole step: fwd (3d-2) P + bwd (6d-3) P + 8 N_b F_b + O(N_a h)."""
+    P, Q = 4.0 * Nb * h, 4.0 * Na * h
+    steps = max(d - 1, 1)
+    depth_avg = ((2 * P) + (d - 2) * 3 * P) / steps + 16.0 * Nb + 4.0 * Na + 4.0 * h * h if d > 1 else 0.0
+    step = ((3 * d - 2) + (6 * d - 3)) * P + 8.0 * Nb * Fb + 8.0 * Na * Fa + 6 * Q + 8.0 * G * h
+    return {"depth_step": depth_avg, "step": step}
+
+
+def contract_flops(Na, Nb, h, Fa, Fb, d):
+    """SURVEY.md section 8(d) "Algorithmic flops" (padding and the 3xTF32 correction passes are NOT credited)."""
+    fwd = 2.0 * h * (Nb * Fb + (d - 1) * Nb * h + Na * (Fa + h))
+    bwd = 2.0 * h * (Nb * Fb + 2 * (d - 1) * Nb * h + Na * (Fa + h) + Na * h)
+    return {"step": fwd + bwd, "depth_step": 2.0 * Nb * h * h}
+
+
+def measure_tf32_peak(dev):
+    """Dense TF32 tensor throughput the way MEASURED_PEAKS.json measures bf16: torch.matmul (cuBLAS) 8192^3 with
+    allow_tf32, best of 10, CUDA events.  A yardstick for the tensor-bound configuration only; not on the product path."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n = 8192
+        x, y = torch.randn(n, n, device=dev), torch.randn(n, n, device=dev)
+        best = 1e9
+        for i in range(12):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch.matmul(x, y)
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                best = min(best, e0.elapsed_time(e1))
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
 
 
 def measured_traffic(a, category):
@@ -521,25 +599,43 @@ def main():
                 "peak_source": peak_src, "ms_per_launch": kernels[dom]["ms_per_launch"],
                 "alg_bytes_per_launch": alg[dom]}
         step_bytes = sum(alg[k] * v["launches_per_step"] for k, v in kernels.items())
+        # the contract's own byte / flop counts next to the as-implemented ones
+        cb = contract_bytes(Na, Nb, G, a.hidden, bmg.atom_fdim, bmg.bond_fdim, a.depth)
+        cf = contract_flops(Na, Nb, a.hidden, bmg.atom_fdim, bmg.bond_fdim, a.depth)
+        roof["alg_bytes_source"] = "as implemented (DESIGN.md 4.1); frac_contract uses SURVEY.md 8(d)'s bytes"
+        if dom == "depth_step" and cb["depth_step"]:
+            roof["contract_bytes_per_launch"] = cb["depth_step"]
+            roof["frac_contract"] = cb["depth_step"] / (kernels[dom]["ms_per_launch"] * 1e-3) / 1e9 / peak
+        step_tensor = None
+        if cf["step"] / cb["step"] > 150.0:        # above the TF32 ridge (~100-170 flop/B): tensor-bound (BASELINE configs[3])
+            tf32_peak = measure_tf32_peak(dev)
+            per = kernels["depth_step"]["ms_per_launch"]
+            ach = cf["depth_step"] / (per * 1e-3) / 1e12
+            roof = {"kernel": "depth_step", "bound": "tensor", "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s",
+                    "frac": ach / tf32_peak, "traffic": None, "ms_per_launch": per,
+                    "peak_source": "measured here: torch.matmul fp32 with allow_tf32, 8192^3, best of 10 (burst), the way "
+                                   "MEASURED_PEAKS.json measures bf16", "flops_per_launch": cf["depth_step"]}
+            step_tensor = {"flops": cf["step"], "achieved_tflops": cf["step"] / (ms_step * 1e-3) / 1e12,
+                           "frac": cf["step"] / (ms_step * 1e-3) / 1e12 / tf32_peak}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
                 "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "ms_per_step_with_events": ms_step_events,
                 "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None,
                 "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[a.math],
                 "data": "synthetic",
-                "config": {"workload": workload_name(a), "global_batch": world * G, "n_atoms": Na, "n_bonds": Nb,
-                           "parallelism": f"dp{world}" if world > 1 else "single GPU",
-                           "l2": "per-step working set (workspace >= 2 GB at batch 4096) exceeds the 126 MB L2",
-                           "math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0", "sign_bits": sign_bits},
+                "config": base_config(a, world, G, Na, Nb),
+                "options": {"math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0", "sign_bits": sign_bits},
                 "edge_msgs_per_s": world * (Nb - 1) * max(a.depth - 1, 0) / (ms_step * 1e-3),
                 "roofline": roof, "kernels": kernels,
                 "step_hbm": {"alg_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,
-                             "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
+                             "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak,
+                             "contract_bytes": cb["step"], "frac_contract": cb["step"] / (ms_step * 1e-3) / 1e9 / peak},
+                "step_tensor": step_tensor,
                 "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "e2e_full_tensors": e2e_full,
                 "e2e_device_store": e2e_store, "e2e_host_waits_for_backward": e2e_step_sync,
                 "optimizer_step": optimizer_step, "inference": inference}
         if not a.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(graphs, a)
+            line["cpu_baseline"] = cpu_baseline(graphs, a, steps=10, warmup=2, extras=True)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -67,7 +67,8 @@ def dropout_multiplier(n_rows: int, n_cols: int, ld: int, p: float, seed_lo: int
 
 def encoder_forward(components, weights: Dict[str, torch.Tensor], depth: int,
                     activation: str = "ReLU", undirected: bool = False,
-                    aggregation: str = "mean", aggregation_norm: float = 100.0, dropout=None) -> torch.Tensor:
+                    aggregation: str = "mean", aggregation_norm: float = 100.0, dropout=None,
+                    readout: bool = True) -> torch.Tensor:
     """MPNEncoder.forward, bond-message branch (mpn.py:81-173).  ``dropout`` = None (p = 0 / eval) or a dict
     {p, seed_lo, seed_hi, ld} selecting the product's Philox masks (the reference's own RNG stream cannot be
     shared with a CUDA kernel; the op sequence -- mask * 1/(1-p) after each activation, :124 and :134 -- is the same).
@@ -101,6 +102,8 @@ def encoder_forward(components, weights: Dict[str, torch.Tensor], depth: int,
         atom_hiddens = atom_hiddens * dropout_multiplier(atom_hiddens.shape[0], atom_hiddens.shape[1], dropout["ld"],
                                                          dropout["p"], dropout["seed_lo"], dropout["seed_hi"],
                                                          depth).to(atom_hiddens.dtype)
+    if not readout:          # bench.py's "message passing only" CPU figure: stop before mpn.py:146
+        return atom_hiddens
     mol_vecs = []
     zero = torch.zeros(atom_hiddens.shape[1], dtype=atom_hiddens.dtype)
     for i, (a_start, a_size) in enumerate(a_scope):                                # :147-169
@@ -124,6 +127,8 @@ def encoder_forward_backward(components, weights, d_out, **cfg):
     """Forward + autograd backward on CPU; returns (out, grads-by-name)."""
     ws = {k: v.detach().clone().requires_grad_(True) for k, v in weights.items()}
     out = encoder_forward(components, ws, **cfg)
+    if not cfg.get("readout", True):
+        d_out = torch.ones_like(out)       # backward from atom_hiddens.sum()
     out.backward(d_out)
     return out.detach(), {k: v.grad for k, v in ws.items()}
 
