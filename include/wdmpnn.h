@@ -256,6 +256,21 @@ int64_t wd_adam_scratch_floats(void);
 int wd_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const WdAdam* cfg,
                  float* scratch, float* grad_norm_out, void* stream);
 
+/* wd_adam_step for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arithmetic and arguments as wd_adam_step minus `scratch`: the clipping scratch is a file-scope static device
+ * array inside the library (2 KB per GPU that loads the library, held until the process exits).  The call allocates
+ * nothing (no cudaMalloc / cudaFree / allocating library routine); the caller still owns params, grads and the moments.
+ * Limit: n <= WD_ADAM_STATIC_MAX_PARAMS (wd_adam_static_max_params()), larger n is rejected with WD_ERR_INVALID_ARG.
+ * All calls on one device SHARE the array, which keeps the last call's contents (every slot is rewritten before it is
+ * read, so nothing needs clearing): calls that overlap on the GPU race -- issue them on one stream or order them.
+ * The first call on each device looks the array's device address up (cudaGetSymbolAddress, with that device current);
+ * make that first call outside stream capture. */
+#define WD_ADAM_STATIC_MAX_PARAMS (1LL << 28) /* 268 M fp32 parameters (1 GiB per flat buffer) */
+int64_t wd_adam_static_max_params(void);
+int wd_adam_step_static(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const WdAdam* cfg,
+                        float* grad_norm_out, void* stream);
+
 void wd_profile_enable(int on); /* on != 0: record events around every launch from now on      */
 void wd_profile_reset(void);    /* forget recorded launches (keeps the event pool)              */
 /* Synchronises the recorded events and returns total milliseconds and launch count of category. */

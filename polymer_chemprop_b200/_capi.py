@@ -60,12 +60,13 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_store
            "wd_infer_workspace_bytes", "wd_encoder_infer",
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
-           "wd_debug_dw", "wd_debug_timing", "wd_adam_scratch_floats", "wd_adam_step")
+           "wd_debug_dw", "wd_debug_timing", "wd_adam_scratch_floats", "wd_adam_step", "wd_adam_static_max_params",
+           "wd_adam_step_static")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
-ABI_VERSION = 5      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step,
-                     # 5 = WdConfig.flags, WD_MATH_TF32X3
+ABI_VERSION = 6      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step,
+                     # 5 = WdConfig.flags, WD_MATH_TF32X3, 6 = wd_adam_step_static
 _lib = None
 
 
@@ -93,6 +94,10 @@ def lib():
     L.wd_adam_scratch_floats.restype = C.c_int64
     L.wd_adam_step.argtypes = [vp, vp, vp, vp, C.c_int64, C.POINTER(WdAdam), vp, vp, vp]
     L.wd_adam_step.restype = C.c_int
+    L.wd_adam_static_max_params.argtypes = []
+    L.wd_adam_static_max_params.restype = C.c_int64
+    L.wd_adam_step_static.argtypes = [vp, vp, vp, vp, C.c_int64, C.POINTER(WdAdam), vp, vp]
+    L.wd_adam_step_static.restype = C.c_int
     L.wd_csr_build_check.argtypes = [vp, vp]
     L.wd_csr_build_check.restype = C.c_int
     L.wd_workspace_bytes.argtypes = [C.POINTER(WdConfig), C.c_int64, C.c_int64, C.c_int64]

@@ -6,6 +6,7 @@
 // and the whole update is ONE pass (two more tiny launches when clipping: a fixed-order two-stage sum of squares).
 // HBM-bound byte work: 16 bytes read + 12 written per parameter, float4 per thread.
 #include <cmath>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -112,4 +113,58 @@ extern "C" int wd_adam_step(float* params, const float* grads, float* exp_avg, f
   WD_LAUNCH(k_adam_flat, (unsigned)ceil_div(ceil_div(n, 4), 256), 256, 0, s, params, grads, exp_avg, exp_avg_sq, n, k,
             (const float*)scratch);
   return WD_OK;
+}
+
+// ---- wd_adam_step_static: the same step for callers that cannot allocate (no counterpart in the reference)
+// --------------------------------------------------------------------------------------
+// The clipping scratch (the norm slot + kNormBlocks partial sums of squares) lives in this file-scope device array
+// instead of a caller buffer: 2 KB that every GPU which loads the library holds until the process exits.  In HOST code
+// the array's name is only a host-side stand-in, not a device address, so its device address is looked up once per
+// device -- with that device current -- by cudaGetSymbolAddress and cached; the kernels get that pointer.
+// Every call on a device shares the array and it keeps the last call's contents.  Nothing in it has to start at zero:
+// each call first overwrites all kNormBlocks partials (k_sumsq_partial's grid is fixed), then the norm slot
+// (k_sumsq_final), then reads the norm (k_adam_flat), all stream-ordered.  Calls that OVERLAP on the GPU (different
+// streams without ordering between them, or several host threads) race on the array; serialise them.
+namespace wd {
+namespace {
+
+constexpr int kStaticScratchFloats = 512;
+static_assert(kNormBlocks + 4 <= kStaticScratchFloats, "static scratch too small for the norm partials");
+static __device__ __align__(256) float g_adam_static_scratch[kStaticScratchFloats];
+
+constexpr int kMaxDevices = 64;
+
+int static_scratch(float** out) {
+  static std::mutex mu;
+  static float* ptr[kMaxDevices] = {};
+  int dev = 0;
+  WD_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(WD_ERR_UNSUPPORTED, "wd_adam_step_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {     // once per device, with that device current
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_adam_static_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(WD_ERR_CUDA, "wd_adam_step_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+    ptr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = ptr[dev];
+  return WD_OK;
+}
+
+}  // namespace
+}  // namespace wd
+
+extern "C" int64_t wd_adam_static_max_params(void) { return (int64_t)WD_ADAM_STATIC_MAX_PARAMS; }
+
+extern "C" int wd_adam_step_static(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                   const WdAdam* cfg, float* grad_norm_out, void* stream) {
+  using namespace wd;
+  if (n > (int64_t)WD_ADAM_STATIC_MAX_PARAMS)
+    return fail(WD_ERR_INVALID_ARG, "wd_adam_step_static: n = %lld exceeds the maximum of %lld parameters of the static-scratch "
+                "variant; use wd_adam_step with a caller-provided scratch buffer", (long long)n, (long long)WD_ADAM_STATIC_MAX_PARAMS);
+  float* scratch = nullptr;
+  const int rc = static_scratch(&scratch);
+  if (rc != WD_OK) return rc;
+  return wd_adam_step(params, grads, exp_avg, exp_avg_sq, n, cfg, scratch, grad_norm_out, stream);
 }
