@@ -67,6 +67,26 @@ class MolGraphData:
                 self._prefix_ok = bool(np.array_equal(a, b))
         return self._prefix_ok
 
+    @staticmethod
+    def of(g) -> "MolGraphData":
+        """``g`` itself, or the array form of a REFERENCE ``MolGraph`` (chemprop/features/featurization.py:377-640:
+        Python lists ``f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb`` + ``degree_of_polym``).  The conversion is
+        cached on the object, as the reference caches its MolGraphs in SMILES_TO_GRAPH (data/data.py:30-40), so it is
+        paid once per molecule, not once per batch."""
+        if isinstance(g, MolGraphData):
+            return g
+        cached = getattr(g, "_wd_data", None)
+        if cached is None:
+            cached = MolGraphData(g.f_atoms, g.f_bonds, g.w_atoms, g.w_bonds, g.a2b, g.b2a, g.b2revb,
+                                  getattr(g, "degree_of_polym", 1))
+            cached.overwrite_default_atom_features = getattr(g, "overwrite_default_atom_features", False)
+            cached.overwrite_default_bond_features = getattr(g, "overwrite_default_bond_features", False)
+            try:
+                g._wd_data = cached
+            except AttributeError:
+                pass
+        return cached
+
     def as_reference_lists(self):
         """Duck-typed object with plain Python lists, consumable by the *reference's*
         BatchMolGraph.__init__ (used only by oracle/ scripts and tests)."""
@@ -89,6 +109,9 @@ class BatchMolGraph:
     """
 
     def __init__(self, mol_graphs: Sequence[MolGraphData]):
+        """``mol_graphs``: MolGraphData objects, or the reference's own MolGraph objects (what
+        MoleculeDataset.batch_graph hands over, data/data.py:277-314, once install() has put this class in place)."""
+        mol_graphs = [MolGraphData.of(g) for g in mol_graphs]
         g0 = mol_graphs[0]
         self.overwrite_default_atom_features = g0.overwrite_default_atom_features
         self.overwrite_default_bond_features = g0.overwrite_default_bond_features

@@ -118,6 +118,42 @@ def test_install_makes_the_reference_model_build_this_encoder():
         cm.MPN, cmpn.MPN, cmpn.MPNEncoder = saved
 
 
+def test_install_swaps_batch_mol_graph_and_it_takes_reference_mol_graphs():
+    """install() also puts this package's BatchMolGraph where the reference's loader builds batches
+    (chemprop/data/data.py:312 resolves the name in chemprop.data.data; mol2graph in features.featurization).  Built
+    from the reference's own MolGraph-style objects (Python lists), it must equal the reference's BatchMolGraph
+    attribute for attribute -- and offer the compact upload form on top."""
+    import importlib
+    from polymer_chemprop_b200 import mpn as ours
+    ref_shim.load_reference()
+    feat = importlib.import_module("chemprop.features.featurization")
+    mods = [importlib.import_module(n) for n in ("chemprop.features.featurization", "chemprop.features", "chemprop.data.data",
+                                                 "chemprop.models.model", "chemprop.models.mpn")]
+    RefBMG = feat.BatchMolGraph
+    graphs = synth.make_graphs("copolymer", 9, 4, random_edge_weights=True) + [synth.empty_graph()] + \
+        synth.make_graphs("qm9", 3, 5)
+    ref_style = [g.as_reference_lists() for g in graphs]          # what MolGraph.__init__ leaves behind: lists
+    ref_bmg = RefBMG(ref_style)
+    saved = [(m, m.BatchMolGraph) for m in mods if hasattr(m, "BatchMolGraph")]
+    saved_mpn = (mods[3].MPN, mods[4].MPN, mods[4].MPNEncoder)
+    try:
+        ours.install()
+        assert all(m.BatchMolGraph is BatchMolGraph for m, _ in saved) and len(saved) >= 3
+        new_bmg = mods[2].BatchMolGraph(ref_style)                # the name data.py:312 resolves
+        a, b = ref_bmg.get_components(), new_bmg.get_components()
+        for x, y in zip(a[:7], b[:7]):
+            assert x.dtype == y.dtype and torch.equal(x, y)
+        assert list(a[7]) == list(b[7]) and list(a[8]) == list(b[8])
+        assert [float(v) for v in a[9]] == [float(v) for v in b[9]]
+        assert (new_bmg.n_atoms, new_bmg.n_bonds, new_bmg.max_num_bonds) == (ref_bmg.n_atoms, ref_bmg.n_bonds, ref_bmg.max_num_bonds)
+        assert new_bmg.f_bonds_tail is not None and new_bmg.a_scope_array is not None      # the compact upload form
+        assert all(hasattr(g, "_wd_data") for g in ref_style)     # converted once per molecule, cached on it
+    finally:
+        for m, v in saved:
+            m.BatchMolGraph = v
+        mods[3].MPN, mods[4].MPN, mods[4].MPNEncoder = saved_mpn
+
+
 def test_noam_lr_oracle_and_mirror_equal_live_reference_scheduler():
     """chemprop/nn_utils.py:115-194 driven as chemprop/train/train.py:82-86 drives it, next to the product's mirror
     and the oracle formula: equal learning rates to the last bit at every step, including the step the base class
