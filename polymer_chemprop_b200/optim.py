@@ -141,43 +141,41 @@ class FlatAdam(torch.optim.Optimizer):
         self.steps = steps
 
 
+def noam_lr_at(step: int, warmup_steps: int, total_steps: int, init_lr: float, max_lr: float, final_lr: float) -> float:
+    """Closed form of the schedule chemprop/nn_utils.py:115-194 walks step by step: linear from ``init_lr`` to ``max_lr``
+    over ``warmup_steps``, then geometric down to ``final_lr`` at ``total_steps``, constant afterwards.  float64
+    scalars in the same operation order as the reference, so the values agree to the last bit (golden-pinned)."""
+    init_lr, max_lr, final_lr = np.float64(init_lr), np.float64(max_lr), np.float64(final_lr)
+    if step <= warmup_steps:
+        return float(init_lr + step * ((max_lr - init_lr) / warmup_steps))
+    if step <= total_steps:
+        return float(max_lr * (((final_lr / max_lr) ** (1 / (total_steps - warmup_steps))) ** (step - warmup_steps)))
+    return float(final_lr)
+
+
 class NoamLR:
-    """chemprop/nn_utils.py:115-194: the learning rate rises linearly from ``init_lr`` to ``max_lr`` over
-    ``warmup_epochs * steps_per_epoch`` steps and then decays exponentially to ``final_lr`` at
-    ``total_epochs * steps_per_epoch``.  Host arithmetic in float64 (numpy), as in the reference."""
+    """Per-step scheduler with the reference NoamLR's constructor and ``step()`` / ``get_lr()`` surface, as a thin
+    driver of ``noam_lr_at``.  (FlatAdam is a torch.optim.Optimizer, so the reference's own NoamLR drives it unchanged;
+    this class exists for callers that run without an importable chemprop.)"""
 
     def __init__(self, optimizer, warmup_epochs: List[Union[float, int]], total_epochs: List[int], steps_per_epoch: int,
                  init_lr: List[float], max_lr: List[float], final_lr: List[float]):
-        if not (len(optimizer.param_groups) == len(warmup_epochs) == len(total_epochs) == len(init_lr) ==
-                len(max_lr) == len(final_lr)):
-            raise ValueError("one entry per parameter group is required")          # nn_utils.py:143-144 asserts
-        self.num_lrs = len(optimizer.param_groups)
-        self.optimizer = optimizer
-        self.warmup_epochs, self.total_epochs = np.array(warmup_epochs), np.array(total_epochs)
-        self.steps_per_epoch = steps_per_epoch
-        self.init_lr, self.max_lr, self.final_lr = np.array(init_lr), np.array(max_lr), np.array(final_lr)
+        groups = optimizer.param_groups
+        if not all(len(x) == len(groups) for x in (warmup_epochs, total_epochs, init_lr, max_lr, final_lr)):
+            raise ValueError("one entry per parameter group is required")
+        self.optimizer, self.steps_per_epoch = optimizer, steps_per_epoch
+        self._plan = [(int(np.float64(w) * steps_per_epoch), t * steps_per_epoch, i, m, f)
+                      for w, t, i, m, f in zip(warmup_epochs, total_epochs, init_lr, max_lr, final_lr)]
         self.current_step = 0
-        self.lr = list(init_lr)
-        self.warmup_steps = (self.warmup_epochs * self.steps_per_epoch).astype(int)
-        self.total_steps = self.total_epochs * self.steps_per_epoch
-        self.linear_increment = (self.max_lr - self.init_lr) / self.warmup_steps
-        self.exponential_gamma = (self.final_lr / self.max_lr) ** (1 / (self.total_steps - self.warmup_steps))
-        for g in self.optimizer.param_groups:
+        self.lr = [float(i) for i in init_lr]
+        for g in groups:
             g.setdefault("initial_lr", g["lr"])
-        self.step()      # torch's _LRScheduler.__init__ (the reference's base class) takes one step: current_step == 1 now
+        self.step()      # torch's _LRScheduler.__init__ (the reference's base class) steps once: current_step == 1 now
 
     def get_lr(self) -> List[float]:
         return list(self.lr)
 
     def step(self, current_step: int = None):
         self.current_step = self.current_step + 1 if current_step is None else current_step
-        s = self.current_step
-        for i, group in enumerate(self.optimizer.param_groups):
-            # scalar float64 arithmetic per group: numpy's array power differs from the scalar one in the last bit
-            if s <= self.warmup_steps[i]:                                            # nn_utils.py:187-188
-                lr = self.init_lr[i] + s * self.linear_increment[i]
-            elif s <= self.total_steps[i]:                                           # :189-190
-                lr = self.max_lr[i] * (self.exponential_gamma[i] ** (s - self.warmup_steps[i]))
-            else:                                                                    # :191-192
-                lr = self.final_lr[i]
-            self.lr[i] = group["lr"] = lr
+        for i, (group, plan) in enumerate(zip(self.optimizer.param_groups, self._plan)):
+            self.lr[i] = group["lr"] = noam_lr_at(self.current_step, *plan)
