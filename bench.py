@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=512, help="graphs in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--store-graphs", type=int, default=None,
+                    help="graphs per rank in the device-resident store (default: the batch at N=1; 125000 at N>1 = "
+                         "BASELINE configs[4]'s 10^6 graphs over 8 GPUs; distinct synthetic graphs are repeated)")
     return ap.parse_args()
 
 
@@ -348,6 +351,70 @@ class HostGraph:
         return self._c
 
 
+class EpochSampler:
+    """Indices of consecutive batches of a freshly shuffled epoch (what the reference's MoleculeSampler does,
+    chemprop/data/data.py:420-470: one permutation per epoch, sliced in order) -- not a new permutation per batch."""
+
+    def __init__(self, n, batch, seed):
+        self.n, self.batch, self.rng, self.perm, self.at = n, batch, np.random.default_rng(seed), None, 0
+
+    def next(self):
+        if self.perm is None or self.at + self.batch > self.n:
+            self.perm, self.at = self.rng.permutation(self.n), 0
+        out = self.perm[self.at:self.at + self.batch]
+        self.at += self.batch
+        return out
+
+
+def run_train_step(a, mpn, params, store, rng, batch, dev, world, copy_stream, sync_all):
+    """"a second line WITH FFN + Adam for the DP config" -- one optimisation step as
+    chemprop/train/train.py:46-86 runs it: batch from the device-resident store -> encoder -> FFN head (model.py:57-116,
+    2 layers, hidden 300, 1 task) -> masked MSE -> backward -> gradient all-reduce -> FlatAdam step."""
+    import torch.distributed as dist
+    import torch.nn as nn
+    from polymer_chemprop_b200 import FlatAdam, dp
+    torch.manual_seed(1)
+    ffn = nn.Sequential(nn.Dropout(0.0), nn.Linear(a.hidden, 300), nn.ReLU(), nn.Dropout(0.0), nn.Linear(300, 1)).to(dev)
+    allp = list(params) + list(ffn.parameters())
+    reducer = dp.FlatGradAllReduce(allp) if world > 1 else None
+    if reducer is not None:
+        reducer.attach(mpn)
+    opt = FlatAdam(allp, lr=1e-4, grad_buffer=reducer)
+    targets = torch.randn(batch, 1, device=dev)
+    mask = torch.ones(batch, 1, device=dev)
+    state = {"next": store.batch(rng.next(), stream=copy_stream)}
+
+    def one():
+        cur = state["next"]
+        state["next"] = store.batch(rng.next(), stream=copy_stream)
+        for p in allp:
+            p.grad = None
+        preds = ffn(mpn([cur]))
+        loss = (nn.functional.mse_loss(preds, targets, reduction="none") * mask).sum() / mask.sum()
+        loss.backward()
+        if reducer is not None:
+            reducer()
+        opt.step()
+        return loss
+
+    for _ in range(5):
+        one()
+    sync_all()
+    k = max(3, min(a.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(k):
+        loss = one()
+    float(loss.detach())                          # the step's loss reaches the host
+    sync_all()
+    te = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    if reducer is not None:
+        reducer.detach()
+    return {"value": world * batch / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()), "steps": k,
+            "what": "store batch -> MPN -> FFN(300, 1) -> masked MSE -> backward -> all-reduce -> FlatAdam, wall clock"}
+
+
 def main():
     a = parse_args()
     if a.impl == "reference":
@@ -377,6 +444,8 @@ def main():
 
     from polymer_chemprop_b200 import dp
     reducer = dp.FlatGradAllReduce(params) if world > 1 else None
+    if reducer is not None:
+        reducer.attach(model)      # wd_encoder_backward writes straight into the flat buffer: no pack / unpack kernels
 
     def step():
         for p in params:
@@ -431,6 +500,22 @@ def main():
     lib.wd_profile_reset()
     value = world * G / (ms_step * 1e-3)
 
+    # ---- share of the step spent in the gradient all-reduce (SURVEY.md 8(e) "Report"): the collective alone, back to back
+    allreduce = None
+    if world > 1:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync_all()
+        e0.record()
+        for _ in range(a.steps):
+            reducer()
+        e1.record()
+        sync_all()
+        t = torch.tensor([e0.elapsed_time(e1) / a.steps], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        allreduce = {"ms_per_step": float(t.item()), "bytes": reducer.nbytes, "share_of_step": float(t.item()) / ms_step,
+                     "note": "one ncclAllReduce(avg) of the flat gradient buffer per step, issued after the backward pass; the "
+                             "encoder's backward writes its gradients straight into that buffer"}
+
     # ---- end to end: pinned host tensors -> H2D -> feature expansion + CSR build -> fwd+bwd -> D2H of the output
     e2e, e2e_full, e2e_store, e2e_step_sync = None, None, None, None
     if not a.no_e2e:
@@ -459,7 +544,7 @@ def main():
             before it launches anything of the next step, so the GPU idles during the host's launch prologue."""
             def next_batch():
                 if native == "store":                    # a freshly shuffled batch assembled in HBM from the resident store
-                    return store.batch(store_rng.permutation(len(graphs)), stream=copy_stream)
+                    return store.batch(store_rng.next(), stream=copy_stream)
                 hg = bmg.fresh_view() if native else HostGraph(pinned)
                 DeviceGraph.prefetch(hg, dev, copy_stream)
                 return hg
@@ -517,15 +602,21 @@ def main():
                                "f_bonds rebuilt in HBM by wd_expand_features") if native else
                               "all seven get_components() tensors as they are"}
 
+        train_step = None
         e2e_full = run_e2e(False)
         e2e = run_e2e(True) if bmg.f_bonds_tail is not None else e2e_full
         e2e_step_sync = run_e2e(bmg.f_bonds_tail is not None, sync="step")
         e2e_store = None
         if bmg.f_bonds_tail is not None:
             from polymer_chemprop_b200 import DeviceGraphStore
-            store = DeviceGraphStore(graphs, dev)        # BASELINE configs[4]: "dataset pre-staged on device"
-            store_rng = np.random.default_rng(rank)
+            # BASELINE configs[4] / SURVEY 8(d) config 5: "dataset pre-staged on device", 10^6 graphs over 8 GPUs
+            n_store = a.store_graphs or (125000 if world > 1 else len(graphs))
+            store = DeviceGraphStore(graphs, dev, repeat=max(1, -(-n_store // len(graphs))))
+            store_rng = EpochSampler(len(store), len(graphs), rank)
             e2e_store = run_e2e("store")
+            e2e_store["store_graphs_per_rank"] = len(store)
+            e2e_store["distinct_graphs_per_rank"] = len(graphs)
+            train_step = run_train_step(a, model, params, store, store_rng, len(graphs), dev, world, copy_stream, sync_all)
 
     # ---- forward-only inference path (predict / fingerprint; wd_encoder_infer) ----------------
     inference = None
@@ -633,7 +724,13 @@ def main():
                 "step_tensor": step_tensor,
                 "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e, "e2e_full_tensors": e2e_full,
                 "e2e_device_store": e2e_store, "e2e_host_waits_for_backward": e2e_step_sync,
-                "optimizer_step": optimizer_step, "inference": inference}
+                "optimizer_step": optimizer_step, "inference": inference, "allreduce": allreduce,
+                "train_step": train_step if not a.no_e2e else None}
+        if world > 1 and e2e_store is not None:
+            # data-parallel configuration = BASELINE configs[4]: the dataset is pre-staged on the device, so the end-to-end
+            # figure is the store-fed one; the host-upload loop stays alongside
+            line["e2e_host_upload"] = e2e
+            line["e2e"] = e2e_store
         if not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(graphs, a, steps=10, warmup=2, extras=True)
         print(json.dumps(line), flush=True)

@@ -105,12 +105,33 @@ class DeviceGraphStore:
                     w_bonds=w_bonds, b2a=b2a, b2revb=b2revb, in_idx=in_idx, out_idx=out_idx, in_ptr_local=in_ptr_local,
                     atom_off=atom_off.astype(np.int64), bond_off=bond_off.astype(np.int64), dop=dop)
 
-    def __init__(self, graphs: Sequence[MolGraphData], device: torch.device):
+    @staticmethod
+    def _tile(pk: dict, k: int) -> dict:
+        """The packed store repeated k times (graphs are held in LOCAL numbering, so their arrays tile as they are;
+        only the per-graph offsets continue).  Used to stage datasets of benchmark size -- e.g. BASELINE.json's 10^6
+        graphs -- from a few thousand distinct synthetic graphs without packing each copy in Python."""
+        out = dict(pk)
+        ta, tb = int(pk["atom_off"][-1]), int(pk["bond_off"][-1])
+        for key, rows in (("f_atoms", ta), ("w_atoms", ta), ("in_ptr_local", ta), ("bond_tail", tb), ("w_bonds", tb),
+                          ("b2a", tb), ("b2revb", tb), ("in_idx", tb), ("out_idx", tb)):
+            x = pk[key][:rows]
+            out[key] = np.concatenate([x] * k, axis=0) if rows else pk[key]
+        for key in ("n_atoms_of", "n_bonds_of", "dop"):
+            out[key] = np.tile(pk[key], k)
+        out["atom_off"] = np.concatenate([[0], np.cumsum(out["n_atoms_of"])]).astype(np.int64)
+        out["bond_off"] = np.concatenate([[0], np.cumsum(out["n_bonds_of"])]).astype(np.int64)
+        return out
+
+    def __init__(self, graphs: Sequence[MolGraphData], device: torch.device, repeat: int = 1):
+        """repeat > 1: the store holds ``repeat`` copies of ``graphs`` back to back (index i is graphs[i % len(graphs)])."""
         if device.type != "cuda":
             raise RuntimeError("DeviceGraphStore lives in GPU memory (no CPU fallback)")
-        self.graphs: List[MolGraphData] = list(graphs)
+        base = list(graphs)
         self.device = device
-        pk = self.pack(self.graphs)
+        pk = self.pack(base)
+        if repeat > 1:
+            pk = self._tile(pk, repeat)
+        self.graphs: List[MolGraphData] = base * max(1, repeat)
         self.atom_fdim, self.bond_fdim, self.tail_fdim = pk["atom_fdim"], pk["bond_fdim"], pk["tail_fdim"]
         self.n_atoms_of, self.n_bonds_of = pk["n_atoms_of"], pk["n_bonds_of"]
         self.max_in_degree, self.rev_adjacent = pk["max_in_degree"], pk["rev_adjacent"]

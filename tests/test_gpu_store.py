@@ -57,3 +57,23 @@ def test_encoder_on_an_assembled_batch_equals_the_host_batch_bitwise(mode):
     assert torch.equal(out_s, out_h)
     for k in grads_h:
         assert torch.equal(grads_s[k], grads_h[k]), k
+
+
+def test_repeated_store_assembles_the_same_batches_as_a_store_of_the_copies():
+    """DeviceGraphStore(graphs, repeat=k) (how bench.py stages a dataset of benchmark size) == a store packed from the
+    k copies one by one: same arrays on the host, and a batch drawn across the copies assembles bit-identically."""
+    graphs = _graphs()[:150]
+    tiled = DeviceGraphStore._tile(DeviceGraphStore.pack(graphs), 3)
+    full = DeviceGraphStore.pack(graphs * 3)
+    for k, v in full.items():
+        if isinstance(v, np.ndarray):
+            assert np.array_equal(tiled[k], v), k
+        else:
+            assert tiled[k] == v, k
+    store = DeviceGraphStore(graphs, DEV, repeat=3)
+    assert len(store) == 450
+    idx = np.random.default_rng(5).integers(0, 450, size=200)
+    got = DeviceGraph.get(store.batch(idx), DEV)
+    ref = DeviceGraph(BatchMolGraph([graphs[i % 150] for i in idx]), DEV)
+    for name in ("f_atoms", "f_bonds", "w_bonds", "in_ptr", "src", "rev", "dop"):
+        assert torch.equal(getattr(got, name).view(torch.int32), getattr(ref, name).view(torch.int32)), name
