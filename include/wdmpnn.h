@@ -294,6 +294,11 @@ int wd_debug_timing(uint64_t* out16, int reset);
 const char* wd_last_error(void);
 /* Kernel launches issued by this library since load (for bench.py's gpu_launches). */
 int64_t wd_launch_count(void);
+/* Small batches (n_bonds <= 65536, env WD_GRAPH_MAX_BONDS) run each forward / infer / backward call as ONE CUDA graph
+ * launch: the call's kernels are stream-captured and an executable graph cached per (device, pass, configuration) is
+ * re-parameterised by cudaGraphExecUpdate, see csrc/encoder.cu GraphRun.  launches: graph launches so far; builds: how
+ * many of them had to instantiate a new executable graph (the rest were parameter updates). */
+void wd_graph_stats(int64_t* launches, int64_t* builds);
 /* ABI version of this header. */
 int wd_abi_version(void);
 

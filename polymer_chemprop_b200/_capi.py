@@ -61,7 +61,7 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_store
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
            "wd_debug_dw", "wd_debug_timing", "wd_adam_scratch_floats", "wd_adam_step", "wd_adam_static_max_params",
-           "wd_adam_step_static")
+           "wd_adam_step_static", "wd_graph_stats")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
@@ -98,6 +98,8 @@ def lib():
     L.wd_adam_static_max_params.restype = C.c_int64
     L.wd_adam_step_static.argtypes = [vp, vp, vp, vp, C.c_int64, C.POINTER(WdAdam), vp, vp]
     L.wd_adam_step_static.restype = C.c_int
+    L.wd_graph_stats.argtypes = [C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    L.wd_graph_stats.restype = None
     L.wd_csr_build_check.argtypes = [vp, vp]
     L.wd_csr_build_check.restype = C.c_int
     L.wd_workspace_bytes.argtypes = [C.POINTER(WdConfig), C.c_int64, C.c_int64, C.c_int64]
@@ -156,6 +158,13 @@ def ptr(t):
 
 def current_stream(device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
+
+
+def graph_stats():
+    """(graph launches, executable graphs built) since load: small batches go to the GPU as one CUDA graph per pass."""
+    a, b = C.c_int64(0), C.c_int64(0)
+    lib().wd_graph_stats(C.byref(a), C.byref(b))
+    return a.value, b.value
 
 
 def launch_count() -> int:

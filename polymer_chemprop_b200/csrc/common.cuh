@@ -16,6 +16,7 @@ namespace wd {
 
 extern thread_local char g_err[512];
 extern std::atomic<int64_t> g_launches;
+extern std::atomic<int64_t> g_graph_launches, g_graph_builds;
 
 inline int fail(int code, const char* fmt, ...) {
   va_list ap;

@@ -2,7 +2,10 @@
 // Forward  == chemprop/models/mpn.py:92-171 (bond messages, dropout 0).
 // Backward == autograd of the same, restated as deterministic CSR kernels.
 #include <algorithm>
+#include <array>
 #include <cmath>
+#include <map>
+#include <mutex>
 
 #include "common.cuh"
 #include "graph_kernels.cuh"
@@ -14,6 +17,7 @@ namespace wd {
 
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
+std::atomic<int64_t> g_graph_launches{0}, g_graph_builds{0};
 
 namespace {
 
@@ -471,6 +475,96 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   return red.run(s);
 }
 
+// ---- small batches: one CUDA graph launch per call ---------------------------------------------------------------
+// At the reference's default batch size (50 graphs, chemprop/args.py:95) a forward + backward pass is ~14 us of HBM work
+// behind 26 kernel launches: launch gaps, not the kernels, are the step.  For small batches the call's launches are
+// therefore CAPTURED (stream capture: nothing runs) into a graph, an executable graph of the same topology is re-used
+// through cudaGraphExecUpdate -- pointers, sizes, grids and tensor maps of the new batch replace the old kernel
+// parameters, no re-instantiation -- and the whole pass goes to the GPU as ONE launch.  The cache (one executable
+// graph per device x pass x configuration) is the only state the library keeps besides the error string; it never
+// owns a caller buffer.  Skipped when the caller's stream is itself being captured, under wd_profile_enable (per-launch
+// events), for large batches (nothing to gain: WD_GRAPH_MAX_BONDS, default 65536) and with WD_FLAG_NO_GRAPH.
+constexpr int kRetryEagerly = 1;      // internal: GraphRun::finish could not capture; nothing has run yet
+struct GraphRun {
+  cudaStream_t s;                  // the caller's stream: the graph is LAUNCHED here
+  cudaStream_t cs = nullptr;       // the stream the pass is captured on: a private one, because the caller's stream may be
+  bool active = false;             // the legacy default stream (torch's default), which cannot be captured
+  cudaStream_t stream() const { return active ? cs : s; }      // what the pass must launch on
+  static cudaStream_t capture_stream() {                       // one per host thread and device, created on first use
+    thread_local cudaStream_t st[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return nullptr; }
+    if (st[dev] == nullptr && cudaStreamCreateWithFlags(&st[dev], cudaStreamNonBlocking) != cudaSuccess) {
+      cudaGetLastError();
+      st[dev] = nullptr;
+    }
+    return st[dev];
+  }
+  using Key = std::array<int64_t, 14>;
+  static std::mutex& mu() { static std::mutex m; return m; }
+  static std::map<Key, cudaGraphExec_t>& cache() { static std::map<Key, cudaGraphExec_t> c; return c; }
+  static int64_t max_bonds() {
+    static int64_t v = [] { const char* e = getenv("WD_GRAPH_MAX_BONDS"); return e ? atoll(e) : 65536ll; }();
+    return v;
+  }
+
+  GraphRun(cudaStream_t stream, const WdConfig& c, const WdGraph& g) : s(stream) {
+    if ((c.flags & WD_FLAG_NO_GRAPH) || g_prof_on || g.n_bonds > max_bonds()) return;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess || st != cudaStreamCaptureStatusNone) { cudaGetLastError(); return; }
+    cs = capture_stream();
+    if (cs == nullptr) return;
+    if (cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return; }
+    active = true;
+  }
+  // Ends the capture and launches it.  rc: the result of the captured call (its launches were only recorded).
+  int finish(int rc, int kind, const WdConfig& c, const WdGraph& g) {
+    if (!active) return rc;
+    active = false;
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(cs, &graph);
+    if (e != cudaSuccess || graph == nullptr) {     // something in the pass was not capturable: the caller runs it eagerly
+      cudaGetLastError();
+      if (graph) cudaGraphDestroy(graph);
+      return rc != WD_OK ? rc : kRetryEagerly;
+    }
+    if (rc != WD_OK) { cudaGraphDestroy(graph); return rc; }
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const Key key = {dev, kind, c.hidden_size, c.atom_fdim, c.bond_fdim, c.depth, c.activation, c.aggregation, c.undirected,
+                     c.bias, c.math_mode, (int64_t)c.flags, c.dropout > 0.f ? 1 : 0, g.n_mols > 0 ? 1 : 0};
+    std::lock_guard<std::mutex> lock(mu());
+    auto& cc = cache();
+    cudaGraphExec_t exec = nullptr;
+    auto it = cc.find(key);
+    if (it != cc.end()) {
+      exec = it->second;
+      cudaGraphExecUpdateResultInfo info;
+      if (cudaGraphExecUpdate(exec, graph, &info) != cudaSuccess) {      // topology changed: build a new executable graph
+        cudaGetLastError();
+        cudaGraphExecDestroy(exec);
+        exec = nullptr;
+        cc.erase(it);
+      }
+    }
+    if (exec == nullptr) {
+      if (cc.size() >= 64) { for (auto& kv : cc) cudaGraphExecDestroy(kv.second); cc.clear(); }
+      const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+      if (ei != cudaSuccess) { cudaGraphDestroy(graph); return fail(WD_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ei)); }
+      cc[key] = exec;
+      g_graph_builds.fetch_add(1, std::memory_order_relaxed);
+    }
+    cudaGraphDestroy(graph);
+    const cudaError_t el = cudaGraphLaunch(exec, s);
+    if (el != cudaSuccess) return fail(WD_ERR_CUDA, "cudaGraphLaunch failed: %s", cudaGetErrorString(el));
+    g_graph_launches.fetch_add(1, std::memory_order_relaxed);
+    return WD_OK;
+  }
+  ~GraphRun() {   // an early return between begin and finish must not leave the stream capturing
+    if (active) { cudaGraph_t g = nullptr; cudaStreamEndCapture(cs, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); }
+  }
+};
+
 }  // namespace
 }  // namespace wd
 
@@ -492,7 +586,12 @@ extern "C" int wd_encoder_forward(const WdGraph* graph, const WdWeights* weights
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
   int rc = WD_OK;
-  WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream, false));
+  {
+    GraphRun gr((cudaStream_t)stream, *cfg, *graph);
+    WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, gr.stream(), false));
+    rc = gr.finish(rc, 0, *cfg, *graph);
+  }
+  if (rc == kRetryEagerly) WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream, false));
   return rc;
 }
 
@@ -513,7 +612,12 @@ extern "C" int wd_encoder_infer(const WdGraph* graph, const WdWeights* weights, 
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
   int rc = WD_OK;
-  WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream, true));
+  {
+    GraphRun gr((cudaStream_t)stream, *cfg, *graph);
+    WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, gr.stream(), true));
+    rc = gr.finish(rc, 1, *cfg, *graph);
+  }
+  if (rc == kRetryEagerly) WD_DISPATCH_ACT(cfg->activation, rc = forward_impl<ACT>(*graph, *weights, *cfg, workspace, out, (cudaStream_t)stream, true));
   return rc;
 }
 
@@ -531,13 +635,21 @@ extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weight
   if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0)
     return fail(WD_ERR_INVALID_ARG, "workspace must be 256-byte aligned");
   int rc = WD_OK;
-  WD_DISPATCH_ACT(cfg->activation,
-                  rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, (cudaStream_t)stream));
+  {
+    GraphRun gr((cudaStream_t)stream, *cfg, *graph);
+    WD_DISPATCH_ACT(cfg->activation, rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, gr.stream()));
+    rc = gr.finish(rc, 2, *cfg, *graph);
+  }
+  if (rc == kRetryEagerly) WD_DISPATCH_ACT(cfg->activation, rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, (cudaStream_t)stream));
   return rc;
 }
 
 extern "C" const char* wd_last_error(void) { return wd::g_err; }
 extern "C" int64_t wd_launch_count(void) { return wd::g_launches.load(); }
+extern "C" void wd_graph_stats(int64_t* launches, int64_t* builds) {
+  if (launches) *launches = wd::g_graph_launches.load();
+  if (builds) *builds = wd::g_graph_builds.load();
+}
 
 // ---- test hooks: the raw contractions behind the encoder, on plain operands ----------------------
 // C[M, ldc] = epi(A[M, K] * B^T (+ bias) (+ R)), B(n,k) = b_kn ? W[k*ldb+n] : W[n*ldb+k].

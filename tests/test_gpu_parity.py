@@ -259,3 +259,39 @@ def test_edge_shapes_match_oracle(case, mode, out_tol, grad_tol):
             assert k not in grads
             continue
         assert _golden.rel_err(grads[k], ref) <= grad_tol, k
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
+def test_small_batches_run_as_one_cuda_graph_per_pass_with_the_same_bits(mode, monkeypatch):
+    """Small batches (the reference's default is 50 graphs, chemprop/args.py:95): the library captures each pass into a
+    CUDA graph and re-parameterises ONE executable graph per pass for every new batch (cudaGraphExecUpdate: new
+    pointers, sizes, grids and tensor maps).  Same kernels, same order => bitwise the same results as the plain launches
+    (WD_GRAPH=0 -> WdConfig.flags & WD_FLAG_NO_GRAPH), for batches of different sizes in a row."""
+    batches = [BatchMolGraph(synth.make_graphs("copolymer", n, 200 + n, random_edge_weights=True)) for n in (50, 37, 64)]
+    torch.manual_seed(2)
+    model = _util.MPN(_util.make_args(hidden_size=300, depth=3, wd_math_mode=mode), atom_fdim=batches[0].atom_fdim,
+                      bond_fdim=batches[0].bond_fdim).to(DEV)
+    for p in model.parameters():
+        if p.requires_grad and p.dim() == 2:
+            torch.nn.init.xavier_normal_(p)
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("WD_GRAPH", flag)
+        g0, b0 = _capi.graph_stats()
+        outs = []
+        for bmg in batches:
+            d = torch.randn(len(bmg.a_scope), 300, generator=torch.Generator().manual_seed(3))
+            outs.append(_util.run_fwd_bwd(model, bmg.fresh_view(), d))
+            with torch.no_grad():
+                outs.append((model([bmg.fresh_view()]).cpu(), {}))
+        g1, b1 = _capi.graph_stats()
+        if flag == "1":
+            assert g1 - g0 == 9                      # forward, backward, infer for each of the three batches
+            assert b1 - b0 <= 3                      # at most one executable graph per pass; the rest were updates
+        else:
+            assert g1 == g0
+        res[flag] = outs
+    for (o1, gr1), (o0, gr0) in zip(res["1"], res["0"]):
+        assert torch.equal(o1, o0)
+        for k in gr1:
+            assert torch.equal(gr1[k], gr0[k]), k
