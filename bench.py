@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=512, help="graphs in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-small-batch", action="store_true", help="skip the batch-50 sub-run (key small_batch)")
     ap.add_argument("--store-graphs", type=int, default=None,
                     help="graphs per rank in the device-resident store (default: the batch at N=1; 125000 at N>1 = "
                          "BASELINE configs[4]'s 10^6 graphs over 8 GPUs; distinct synthetic graphs are repeated)")
@@ -349,6 +350,32 @@ class HostGraph:
 
     def get_components(self, atom_messages=False):
         return self._c
+
+
+def small_batch_run(a, cpu):
+    """BASELINE configs[1] also names batch 50 -- the reference's default batch size (chemprop/args.py:95).  The same
+    bench in a child process at --batch 50 (the GPU is idle by now): device-resident `value`, host-buffer `e2e`, the
+    forward-only figure, next to the CPU port timed at batch 50 on this host in this run."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--batch", "50", "--steps", "200", "--warmup", "20", "--hidden",
+           str(a.hidden), "--depth", str(a.depth), "--kind", a.kind, "--math", a.math, "--no-cpu-baseline", "--no-small-batch"]
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+        d = json.loads(out.stdout.strip().splitlines()[-1])
+    except Exception as e:                      # never lose the main line to the side measurement
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
+    res = {"batch": 50, "value": d["value"], "unit": UNIT, "ms_per_step": d["ms_per_step"], "gpu_launches_per_step": d["gpu_launches"] / d["steps"],
+           "graph_launches": d.get("graph_launches"), "n_atoms": d["config"]["n_atoms"], "n_bonds": d["config"]["n_bonds"],
+           "e2e": d["e2e"] and {k: d["e2e"][k] for k in ("value", "ms_per_step", "ms_per_step_median", "h2d_bytes_per_step", "d2h_bytes_per_step")},
+           "e2e_device_store": d["e2e_device_store"] and {k: d["e2e_device_store"][k] for k in ("value", "ms_per_step")},
+           "inference": d["inference"] and {k: d["inference"][k] for k in ("value", "ms_per_step")},
+           "note": "each forward / backward call is ONE CUDA graph launch at this size (csrc/encoder.cu GraphRun); the "
+                   "step is bound by per-kernel latency on the GPU and by Python on the host, not by HBM"}
+    b50 = cpu and cpu.get("other_figures", {}).get("batch_50_all_cores")
+    if b50:
+        res["cpu_port_batch_50"] = {k: b50[k] for k in ("value", "threads", "ms_per_step")}
+        res["value_over_cpu"] = d["value"] / b50["value"]
+        res["e2e_over_cpu"] = d["e2e"]["value"] / b50["value"] if d["e2e"] else None
+    return res
 
 
 class EpochSampler:
@@ -733,6 +760,9 @@ def main():
             line["e2e"] = e2e_store
         if not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(graphs, a, steps=10, warmup=2, extras=True)
+        line["graph_launches"] = dict(zip(("launches", "executable_graphs_built"), _capi.graph_stats()))
+        if world == 1 and a.batch > 50 and not a.no_small_batch and not a.no_e2e:
+            line["small_batch"] = small_batch_run(a, line.get("cpu_baseline"))
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

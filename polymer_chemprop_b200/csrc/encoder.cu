@@ -55,6 +55,20 @@ int sign_words(const TcPacked& B) {
 }
 // infer: forward-only layout (wd_encoder_infer) -- two alternating message buffers, one aggregate buffer, nothing
 // kept for a backward pass (no S_t, no gradient scratch).
+// Column-tile width of a tensor-core contraction over `rows` rows and N output columns.  Large batches take the widest
+// tile the kernel allows (`cap`: every operand row is fetched once).  SMALL batches have fewer 128-row tiles than the
+// GPU has SMs -- 26 at the reference's default batch of 50 graphs -- and a CTA's K loop is a serial chain of load ->
+// transform -> MMA stages, so the kernel's duration is one CTA's latency: there the columns are split over more CTAs
+// (down to 32 columns each) until ~one CTA per SM exists; the re-fetched operand rows are a few hundred KB from L2.
+inline int adaptive_bn(int64_t rows, int N, int cap) {
+  const int64_t m_tiles = ceil_div(std::max<int64_t>(rows, 1), TC_BM);
+  const int np = (int)round_up(N, 16);
+  int n_tiles = (int)ceil_div(np, cap);
+  const int want = (int)std::min<int64_t>(ceil_div(kNumSMs, m_tiles), ceil_div(np, 32));
+  n_tiles = std::max(n_tiles, want);
+  return std::min(cap, (int)round_up(ceil_div(np, n_tiles), 16));
+}
+
 inline bool is_tc(const WdConfig& c) { return c.math_mode == WD_MATH_TF32 || c.math_mode == WD_MATH_TF32X3; }
 
 Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool infer = false) {
@@ -100,11 +114,11 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
   // forward weights: the 3xTF32 mode runs all three contractions on k_tc_gemm4 (tiles up to 304 columns, hi + lo
   // images); the single-pass mode keeps the plain ones on the TMA-fed k_tc_gemm3 (tiles up to 160 columns)
   const int fwd_bn = x3 ? T4_MAX_BN : T2_MAX_BN, parts = x3 ? 2 : 1;
-  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0, fwd_bn, parts);     // I = f_bonds W_i^T
-  L.pWh = tc_packed_geometry(h, h, 0, T4_MAX_BN, parts);            // S W_h^T (gathered depth step)
-  L.pWo = tc_packed_geometry(h, c.atom_fdim, h, fwd_bn, parts);     // [f_atoms, A_d] W_o^T
-  L.pWhT = tc_packed_geometry(h, h, 0);              // dS = dZ W_h           (backward: single-pass TF32 in both modes)
-  L.pWoT = tc_packed_geometry(h, h, 0);              // dA_d = dZo W_o[:, F_a:]
+  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0, adaptive_bn(Nb, h, fwd_bn), parts);     // I = f_bonds W_i^T
+  L.pWh = tc_packed_geometry(h, h, 0, adaptive_bn(Nb, h, T4_MAX_BN), parts);            // S W_h^T (gathered depth step)
+  L.pWo = tc_packed_geometry(h, c.atom_fdim, h, adaptive_bn(Na, h, fwd_bn), parts);     // [f_atoms, A_d] W_o^T
+  L.pWhT = tc_packed_geometry(h, h, 0, adaptive_bn(Nb, h, T2_MAX_BN));   // dS = dZ W_h     (backward: single-pass TF32 in both modes)
+  L.pWoT = tc_packed_geometry(h, h, 0, adaptive_bn(Na, h, T2_MAX_BN));   // dA_d = dZo W_o[:, F_a:]
   // the message gradient only needs (y > 0) of a ReLU output: the tensor-core epilogues leave those bits behind
   // (decided by the config alone, so that the forward and the backward call of one step cannot disagree)
   L.sign_ld = 0;

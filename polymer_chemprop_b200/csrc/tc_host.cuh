@@ -196,7 +196,7 @@ inline int tc_dw_count_tiles(int w0, int w1) {
 inline int tc_dw_z(int64_t rows, int n1, int n2_tiles) {
   const int64_t ctas = ceil_div(n1, D4_MROWS) * std::max(1, n2_tiles);
   int64_t z = std::max<int64_t>(1, kNumSMs / ctas);
-  z = std::min<int64_t>(z, std::max<int64_t>(1, rows / 128));
+  z = std::min<int64_t>(z, std::max<int64_t>(1, rows / 64));    // small batches: chunks of >= 64 rows keep every SM busy
   z = std::min<int64_t>(z, kNumSMs);
   const int64_t rpz = round_up(ceil_div(rows, z), TC_BK);
   return (int)ceil_div(rows, rpz);

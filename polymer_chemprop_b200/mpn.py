@@ -40,7 +40,7 @@ class DeviceGraph:
         """``stream``: build on that CUDA stream without blocking the host (pinned host tensors are
         copied with non_blocking=True); consumers wait on ``self.ready``.  Validation of the graph
         invariants is deferred to ``check()`` (first use), which only waits for this graph's own work."""
-        with torch.cuda.device(device):     # the library launches on the current device (the reference never sets it)
+        with _capi.device_guard(device):     # the library launches on the current device (the reference never sets it)
             if stream is not None:
                 with torch.cuda.stream(stream):
                     self._build(mol_graph, device, non_blocking=True)
@@ -202,7 +202,7 @@ class _EncoderFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, enc, dg, cfg, W_i, b_i, W_h, b_h, W_o, b_o):
         dev = dg.device
-        with torch.cuda.device(dev):        # the library launches on the CURRENT device: the reference never calls set_device
+        with _capi.device_guard(dev):        # the library launches on the CURRENT device: the reference never calls set_device
             ws_bytes = _capi.lib().wd_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
             if ws_bytes == 0:
                 _capi.check(_capi.WD_ERR_INVALID_ARG)
@@ -231,7 +231,7 @@ class _EncoderFunction(torch.autograd.Function):
         saved = iter(ctx.saved_tensors)                     # raises if a parameter was modified in place since forward
         W_i, b_i, W_h, b_h, W_o, b_o = [next(saved).detach().contiguous() if here else None for here in ctx.present]
         sink = enc._grad_sink
-        with torch.cuda.device(dev):
+        with _capi.device_guard(dev):
             d_out = d_out.contiguous().float()
             direct = sink is not None and sink.take(enc)    # first backward of this encoder in the step: write in place
             if direct:
@@ -319,7 +319,7 @@ class MPNEncoder(nn.Module):
         """Forward only (torch.no_grad(): chemprop/train/predict.py:10-68, molecule_fingerprint.py:151-183):
         wd_encoder_infer keeps nothing for a backward pass, so the workspace is a third of the training one."""
         L, dev = _capi.lib(), dg.device
-        with torch.cuda.device(dev):
+        with _capi.device_guard(dev):
             ws_bytes = L.wd_infer_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
             if ws_bytes == 0:
                 _capi.check(_capi.WD_ERR_INVALID_ARG)

@@ -113,7 +113,7 @@ class FlatAdam(torch.optim.Optimizer):
                            float(g["weight_decay"]), float(self.max_grad_norm) if self.max_grad_norm else 0.0,
                            self.steps, int(self.decoupled))
         p = _capi.ptr
-        with torch.cuda.device(self.flat_params.device):    # the library launches on the current device
+        with _capi.device_guard(self.flat_params.device):    # the library launches on the current device
             _capi.check(_capi.lib().wd_adam_step(p(self.flat_params), p(self.flat_grads), p(self.exp_avg), p(self.exp_avg_sq),
                                                  self.flat_params.numel(), C.byref(cfg), p(self._scratch), p(self.grad_norm),
                                                  _capi.current_stream(self.flat_params.device)))

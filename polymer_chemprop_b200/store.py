@@ -173,7 +173,7 @@ class DeviceGraphStore:
         idx = np.ascontiguousarray(np.asarray(indices, dtype=np.int64).reshape(-1))
         if idx.size == 0 or idx.min() < 0 or idx.max() >= len(self.graphs):
             raise ValueError("indices out of range or empty")
-        with torch.cuda.device(self.device):    # the library launches on the current device
+        with _capi.device_guard(self.device):    # the library launches on the current device
             if stream is not None:
                 with torch.cuda.stream(stream):
                     dg = self._assemble(idx)

@@ -1,0 +1,15 @@
+#!/bin/bash
+set -u
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -x -q -m gpu -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log | cut -c1-250
+for m in fp32 tf32 tf32x3; do echo "== $m"; WDMPNN_MATH=$m timeout 200 python scripts/b50_host_profile.py 2>&1 | head -6; done
+echo "== B=512"; for m in fp32 tf32x3; do WDMPNN_MATH=$m timeout 200 python scripts/b50_host_profile.py 512 2>&1 | head -3 | tail -2; done
+timeout 300 python bench.py --steps 200 --warmup 20 --batch 50 --no-cpu-baseline > gpurun_out/bench_b50.json 2> gpurun_out/bench_b50.err; echo "rc=$?"
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-e2e > gpurun_out/bench_b4096.json 2> gpurun_out/bench_b4096.err; echo "rc=$?"
+python - <<'PY'
+import json
+for f in ("bench_b50", "bench_b4096"):
+    d = json.loads(open(f"gpurun_out/{f}.json").read().strip().splitlines()[-1])
+    print(f, round(d["value"]), "graphs/s", round(d["ms_per_step"], 4), "ms; infer", round(d["inference"]["value"]), "e2e", d["e2e"] and round(d["e2e"]["value"]))
+    print("   ", " ".join(f"{k}={v['ms_per_launch']*1e3:.1f}x{v['launches_per_step']:.0f}" for k, v in d["kernels"].items()))
+PY
