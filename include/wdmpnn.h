@@ -271,6 +271,40 @@ int64_t wd_adam_static_max_params(void);
 int wd_adam_step_static(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const WdAdam* cfg,
                         float* grad_norm_out, void* stream);
 
+/* ---- FFN head + masked MSE loss on the encoder output ------------------------------------------
+ * MoleculeModel.ffn (chemprop/models/model.py:57-116: Sequential[Dropout, Linear, (act, Dropout, Linear)*], forward
+ * :174-194) and the regression loss of chemprop/train/train.py:46-74,
+ *   loss = sum((preds - targets)^2 * weights * mask) / sum(mask),     weights = target_weights * data_weights,
+ * as two calls over caller-owned buffers (fp32 CUDA-core contractions, deterministic).  Dropout must be off.
+ * nn.Linear layout: W[l] is [out_l, in_l] row-major, b[l] is [out_l]; layer 0 reads in_dim columns, the last layer writes
+ * out_dim (= num_tasks), every layer in between is hidden_dim wide. */
+#define WD_HEAD_MAX_LAYERS 8
+typedef struct WdHead {
+  int32_t n_layers;    /* args.ffn_num_layers                                   */
+  int32_t activation;  /* WD_ACT_* (args.activation)                            */
+  int32_t in_dim;      /* first_linear_dim (model.py:68-76)                     */
+  int32_t hidden_dim;  /* args.ffn_hidden_size                                  */
+  int32_t out_dim;     /* output_size = num_tasks                               */
+  const float* W[WD_HEAD_MAX_LAYERS];
+  const float* b[WD_HEAD_MAX_LAYERS];
+} WdHead;
+typedef struct WdHeadGrads { /* same shapes as the weights; OVERWRITTEN */
+  float* dW[WD_HEAD_MAX_LAYERS];
+  float* db[WD_HEAD_MAX_LAYERS];
+} WdHeadGrads;
+size_t wd_head_workspace_bytes(const WdHead* head, int64_t n_rows);
+/* preds[n_rows, out_dim] = ffn(X[n_rows, ldx]).  With targets != NULL (training): also loss[0] (DEVICE float) and, kept
+ * in the workspace for wd_head_backward, the layer outputs and d loss / d preds; weights may be NULL (all ones);
+ * targets / weights / mask are dense [n_rows, out_dim] floats (mask: 1 where a target is present). */
+int wd_head_forward(const WdHead* head, const float* X, int32_t ldx, int64_t n_rows, const float* targets,
+                    const float* weights, const float* mask, void* workspace, size_t workspace_bytes, float* preds,
+                    float* loss, void* stream);
+/* Gradients of (dloss[0] * loss + sum(dpreds * preds)) w.r.t. every W[l], b[l] and X (dX[n_rows, lddx], may be NULL;
+ * lddx >= in_dim, a multiple of 4, base 16-byte aligned: rows are written as float4, pad columns as zeros);
+ * dloss (DEVICE float) NULL means 1, dpreds NULL means 0.  Same workspace as the forward call, untouched in between. */
+int wd_head_backward(const WdHead* head, const float* X, int32_t ldx, int64_t n_rows, void* workspace, size_t workspace_bytes,
+                     const float* dloss, const float* dpreds, float* dX, int32_t lddx, const WdHeadGrads* grads, void* stream);
+
 void wd_profile_enable(int on); /* on != 0: record events around every launch from now on      */
 void wd_profile_reset(void);    /* forget recorded launches (keeps the event pool)              */
 /* Synchronises the recorded events and returns total milliseconds and launch count of category. */

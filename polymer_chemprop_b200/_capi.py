@@ -48,6 +48,18 @@ class WdStore(C.Structure):
                                           "in_ptr_local", "atom_off", "bond_off", "dop")]
 
 
+HEAD_MAX_LAYERS = 8
+
+
+class WdHead(C.Structure):
+    _fields_ = [("n_layers", C.c_int32), ("activation", C.c_int32), ("in_dim", C.c_int32), ("hidden_dim", C.c_int32),
+                ("out_dim", C.c_int32), ("W", C.c_void_p * HEAD_MAX_LAYERS), ("b", C.c_void_p * HEAD_MAX_LAYERS)]
+
+
+class WdHeadGrads(C.Structure):
+    _fields_ = [("dW", C.c_void_p * HEAD_MAX_LAYERS), ("db", C.c_void_p * HEAD_MAX_LAYERS)]
+
+
 class WdWeights(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("W_i", "b_i", "W_h", "b_h", "W_o", "b_o")]
 
@@ -61,12 +73,12 @@ EXPORTS = ("wd_csr_build", "wd_csr_build_check", "wd_expand_features", "wd_store
            "wd_encoder_backward", "wd_encoder_host", "wd_last_error", "wd_launch_count",
            "wd_abi_version", "wd_profile_enable", "wd_profile_reset", "wd_profile_read", "wd_debug_gemm",
            "wd_debug_dw", "wd_debug_timing", "wd_adam_scratch_floats", "wd_adam_step", "wd_adam_static_max_params",
-           "wd_adam_step_static", "wd_graph_stats")
+           "wd_adam_step_static", "wd_graph_stats", "wd_head_workspace_bytes", "wd_head_forward", "wd_head_backward")
 PROF_CATEGORIES = ("input_proj", "aggregate", "depth_step", "atom_update", "readout", "msg_grad", "dw",
                    "dx", "scatter", "misc", "reduce")
 
-ABI_VERSION = 6      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step,
-                     # 5 = WdConfig.flags, WD_MATH_TF32X3, 6 = wd_adam_step_static
+ABI_VERSION = 7      # include/wdmpnn.h: 2 = WdGraph gained ld_atoms / ld_bonds, 3 = wd_expand_features, 4 = wd_adam_step,
+                     # 5 = WdConfig.flags, WD_MATH_TF32X3, 6 = wd_adam_step_static, 7 = wd_head_*, wd_graph_stats
 _lib = None
 
 
@@ -98,6 +110,13 @@ def lib():
     L.wd_adam_static_max_params.restype = C.c_int64
     L.wd_adam_step_static.argtypes = [vp, vp, vp, vp, C.c_int64, C.POINTER(WdAdam), vp, vp]
     L.wd_adam_step_static.restype = C.c_int
+    L.wd_head_workspace_bytes.argtypes = [C.POINTER(WdHead), C.c_int64]
+    L.wd_head_workspace_bytes.restype = C.c_size_t
+    L.wd_head_forward.argtypes = [C.POINTER(WdHead), vp, C.c_int32, C.c_int64, vp, vp, vp, vp, C.c_size_t, vp, vp, vp]
+    L.wd_head_forward.restype = C.c_int
+    L.wd_head_backward.argtypes = [C.POINTER(WdHead), vp, C.c_int32, C.c_int64, vp, C.c_size_t, vp, vp, vp, C.c_int32,
+                                   C.POINTER(WdHeadGrads), vp]
+    L.wd_head_backward.restype = C.c_int
     L.wd_graph_stats.argtypes = [C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     L.wd_graph_stats.restype = None
     L.wd_csr_build_check.argtypes = [vp, vp]

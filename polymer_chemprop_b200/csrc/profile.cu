@@ -71,4 +71,4 @@ extern "C" int wd_profile_read(int category, double* total_ms, int64_t* launches
 
 // ABI version of include/wdmpnn.h (3: wd_expand_features, wd_encoder_infer, wd_store_assemble, WdConfig.dropout*, WdGraph.rev_adjacent;
 // 4: wd_adam_step)
-extern "C" int wd_abi_version(void) { return 6; }
+extern "C" int wd_abi_version(void) { return 7; }

@@ -176,7 +176,7 @@ k_simt_dw(const float* __restrict__ X, int ldx, AOperand Y, float* __restrict__ 
 }
 
 // column sums over a row chunk: P[z][n] = sum_{r in chunk z} X[r, n]   (bias gradients)
-__global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __restrict__ P,
+static __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, float* __restrict__ P,
                                  int64_t R, int N, int64_t rows_per_chunk) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -211,7 +211,7 @@ struct ReduceJobs {
   ReduceJob j[RP_MAX_JOBS];
   int count;
 };
-__global__ void __launch_bounds__(RP_COLS * RP_GROUPS) k_reduce_partials(const ReduceJobs jobs) {
+static __global__ void __launch_bounds__(RP_COLS * RP_GROUPS) k_reduce_partials(const ReduceJobs jobs) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   __shared__ float part[RP_GROUPS][RP_COLS];
   int ji = 0;
