@@ -122,6 +122,19 @@ __device__ __forceinline__ void tc_issue_chunk(uint32_t a_addr, uint32_t b_addr,
   }
 }
 
+// the same K chunk issued from convergent code (all lanes call it; the election is inside every statement: tc_ptx.cuh)
+__device__ __forceinline__ void tc_issue_chunk_elect(uint32_t a_addr, uint32_t b_addr, uint32_t d_tmem, int BN, bool first_chunk) {
+  const int N1 = BN > 256 ? 256 : BN, N2 = BN - N1;
+  const uint32_t id1 = ptx::idesc_tf32(128, N1), id2 = ptx::idesc_tf32(128, N2);
+  const uint32_t a_lo = ptx::desc_lo_sw128(a_addr), b_lo = ptx::desc_lo_sw128(b_addr), b2_lo = ptx::desc_lo_sw128(b_addr + N1 * 128);
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks) {
+    const uint32_t acc = (first_chunk && ks == 0) ? 0u : 1u;
+    ptx::mma_elect<false>(d_tmem, a_lo + 2 * ks, b_lo + 2 * ks, ptx::kDescHiSw128, id1, acc);
+    if (N2 > 0) ptx::mma_elect<false>(d_tmem + N1, a_lo + 2 * ks, b2_lo + 2 * ks, ptx::kDescHiSw128, id2, acc);
+  }
+}
+
 // One tile of the Y operand of a weight-gradient contraction (tc_dw4.cuh / tc_dw5.cuh).
 constexpr int TC_DW_MAX_TILES = 24;
 struct TcDwTile {

@@ -66,6 +66,11 @@ __device__ __forceinline__ uint64_t smem_desc_mn32(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)1 << 61;              // SWIZZLE_128B_BASE32B
   return d;
 }
+// the same descriptor as (low word, constant high word) for the convergent issue path (tc_ptx.cuh: mma_elect)
+__device__ __forceinline__ uint32_t desc_lo_mn32(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+constexpr uint32_t kDescHiMn32 = (512u >> 4) | (1u << 14) | (1u << 29);
 __host__ __device__ inline uint32_t idesc_tf32_mn(int M, int N) { return ptx::idesc_tf32(M, N) | (1u << 15) | (1u << 16); }
 
 // Store-only epilogue of one 128 x BN accumulator (partial tile): as tc_epilogue, but the write-out loop is

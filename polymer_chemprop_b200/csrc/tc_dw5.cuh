@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(D5_THREADS, 1) k_tc_dw5(const __grid_constant_
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   constexpr int BK = D5_BK, BLK = BK * 128;                                   // bytes of one 32-column block
   extern __shared__ uint8_t smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = ptx::uniform_warp_idx(), lane = threadIdx.x & 31;   // provably warp-uniform: see tc_ptx.cuh
   const uint32_t base = ptx::smem_u32(smem_raw);
   uint8_t* ring = smem_raw + (((base + 1023u) & ~1023u) - base);
   const int XB = p.XB, YB = p.YB, SR = p.stages;
@@ -84,23 +84,22 @@ __global__ void __launch_bounds__(D5_THREADS, 1) k_tc_dw5(const __grid_constant_
   if (warp == D5_MMA_WARP) {
     // ================= MMA issue =================
     const uint32_t idesc = idesc_tf32_mn(128, tl.BN);
-    const uint32_t ring_u32 = ptx::smem_u32(ring);
+    const uint32_t ring_u32 = ptx::uniform_u32(ptx::smem_u32(ring)), tmem_u = ptx::uniform_u32(tmem_base);
     for (int kc = 0; kc < KC; ++kc) {
       const int s = kc % SR;
       T2_WAIT(5, &bar->full[s], (kc / SR) & 1);
       ptx::tc_fence_after();
-      if (lane == 0) {
-        const uint32_t xa = ring_u32 + s * stage_bytes, ya = xa + x_bytes;
+      // convergent issue (the election is inside every statement); K group g = 8 rows = 1024 bytes = +64 in the low word
+      const uint32_t xa = desc_lo_mn32(ring_u32 + s * stage_bytes, (uint32_t)BLK);
+      const uint32_t ya = desc_lo_mn32(ring_u32 + s * stage_bytes + x_bytes, (uint32_t)BLK);
 #pragma unroll
-        for (int g = 0; g < BK / 8; ++g) {
-          const uint64_t bd = smem_desc_mn32(ya + g * 1024, (uint32_t)BLK);
-          const uint32_t acc = (kc == 0 && g == 0) ? 0u : 1u;
-          for (int mt = 0; mt < n_mt; ++mt)
-            ptx::mma_tf32(tmem_base + mt * D4_ACC_COLS, smem_desc_mn32(xa + mt * 4 * BLK + g * 1024, (uint32_t)BLK), bd, idesc, acc);
-        }
-        ptx::tc_commit(&bar->empty[s]);
-        if (kc == KC - 1) ptx::tc_commit(&bar->tmem_full);
+      for (int g = 0; g < BK / 8; ++g) {
+        const uint32_t acc = (kc == 0 && g == 0) ? 0u : 1u;
+        for (int mt = 0; mt < n_mt; ++mt)
+          ptx::mma_elect<false>(tmem_u + mt * D4_ACC_COLS, xa + ((mt * 4 * BLK) >> 4) + g * 64, ya + g * 64, kDescHiMn32, idesc, acc);
       }
+      ptx::tc_commit_elect(&bar->empty[s]);
+      if (kc == KC - 1) ptx::tc_commit_elect(&bar->tmem_full);
       __syncwarp();
     }
   } else if (warp == D5_TMA_WARP) {

@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   static_assert(EPI != E_RES_ACT, "the residual epilogue belongs to the gathered kernel");
   extern __shared__ uint8_t smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = ptx::uniform_warp_idx(), lane = threadIdx.x & 31;   // provably warp-uniform: see tc_ptx.cuh
   const uint32_t base = ptx::smem_u32(smem_raw);
   uint8_t* ops = smem_raw + (((base + 1023u) & ~1023u) - base);        // 1024-aligned
   const int b_stage = p.BN * 128, stage = TC_A_STAGE + b_stage;          // multiples of 1024 (BN % 16 == 0 -> 2048)
@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
   } else if (warp == T2_MMA_WARP) {
     // ================= MMA issue =================
     uint32_t it = 0, tl = 0;
+    const uint32_t ops_u = ptx::uniform_u32(ptx::smem_u32(ops)), tmem_u = ptx::uniform_u32(tmem_base);
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x, ++tl) {
       const int acc = tl & 1;
       T2_WAIT(4, &bar->tmem_empty[acc], ((tl >> 1) & 1) ^ 1);
@@ -161,12 +162,10 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
         const int s = it % T3_STAGES;
         T2_WAIT(5, &bar->full[s], (it / T3_STAGES) & 1);
         ptx::tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = ptx::smem_u32(ops + s * stage);
-          tc_issue_chunk(a_addr, a_addr + TC_A_STAGE, tmem_base + acc * 256, p.BN, kc == 0);
-          ptx::tc_commit(&bar->empty[s]);
-          if (kc == p.KC - 1) ptx::tc_commit(&bar->tmem_full[acc]);
-        }
+        const uint32_t a_addr = ops_u + s * stage;         // convergent issue: the election is inside every statement
+        tc_issue_chunk_elect(a_addr, a_addr + TC_A_STAGE, tmem_u + acc * 256, p.BN, kc == 0);
+        ptx::tc_commit_elect(&bar->empty[s]);
+        if (kc == p.KC - 1) ptx::tc_commit_elect(&bar->tmem_full[acc]);
         __syncwarp();
       }
     }

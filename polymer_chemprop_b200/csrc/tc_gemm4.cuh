@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
   constexpr bool GATHER = AMODE == A_GATHER_DIFF;
   static_assert(GATHER || !PREACT, "PREACT belongs to the gathered operand");
   extern __shared__ uint8_t smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = ptx::uniform_warp_idx(), lane = threadIdx.x & 31;   // provably warp-uniform: see tc_ptx.cuh
   const uint32_t base = ptx::smem_u32(smem_raw);
   uint8_t* ringA = smem_raw + (((base + 1023u) & ~1023u) - base);      // 1024-aligned
   const int b_stage = p.BN * 128;
@@ -426,6 +426,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
   } else if (warp == T4_MMA_WARP) {
     // ================= MMA issue: two accumulator halves per tile, three rotating TMEM buffers =================
     uint32_t it = 0, g = 0, u = 0;                                      // g: accumulator halves issued so far; u: weight units
+    const uint32_t ringA_u = ptx::uniform_u32(ptx::smem_u32(ringA)), ringB_u = ptx::uniform_u32(ptx::smem_u32(ringB));
+    const uint32_t tmem_u = ptx::uniform_u32(tmem_base);
     const uint32_t idh[2] = {ptx::idesc_tf32(128, W0), ptx::idesc_tf32(128, W1 > 0 ? W1 : 16)};
     const uint32_t idc[2] = {ptx::idesc_bf16(128, W0), ptx::idesc_bf16(128, W1 > 0 ? W1 : 16)};
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
@@ -434,7 +436,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
       for (int kc = 0; kc < p.KC; ++kc, ++it) {
         const int s = it % T4_A_STAGES;
         T2_WAIT(5, &bar->op_full[s], (it / T4_A_STAGES) & 1);
-        const uint32_t a_hi = ptx::smem_u32(ringA + s * T4_A_STAGE), a_lo = a_hi + TC_A_STAGE;
+        const uint32_t a_hi_lo = ptx::desc_lo_sw128(ringA_u + s * T4_A_STAGE);           // low descriptor words of the
+        const uint32_t a_lo_lo = ptx::desc_lo_sw128(ringA_u + s * T4_A_STAGE + TC_A_STAGE);   // a_hi / correction images
         // Issue order: consecutive MMAs alternate between the two accumulator halves (independent chains; measured
         // 3 % faster than half by half).  part 0: a_hi w_hi in kind::tf32.  part 1 (3xTF32): ONE kind::f16 (bf16)
         // group over the correction images, K = 64 per chunk: [bf16 a_lo | bf16 a_hi] . [bf16 w_hi | bf16 w_lo].
@@ -447,33 +450,30 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
             T2_WAIT(6, &bar->b_full[slot], (u / nslots) & 1);
             const uint32_t gb = g0 + hb;
             if (kc == 0 && part == 0) T2_WAIT(4, &bar->tmem_empty[gb % 3], ((gb / 3) & 1) ^ 1);
-            b_addr[hb] = ptx::smem_u32(ringB + (slot / nh) * b_stage + (hb ? W0 * 128 : 0));
-            d[hb] = tmem_base + (gb % 3) * T4_HALF;
+            b_addr[hb] = ptx::desc_lo_sw128(ringB_u + (slot / nh) * b_stage + (hb ? W0 * 128 : 0));
+            d[hb] = tmem_u + (gb % 3) * T4_HALF;
           }
           ptx::tc_fence_after();
-          if (lane == 0) {
-            if (part == 0) {
+          // issued from convergent code, the election is inside each statement (tc_ptx.cuh: mma_elect)
+          if (part == 0) {
 #pragma unroll
-              for (int ks = 0; ks < 4; ++ks)
-                for (int hb = 0; hb < nh; ++hb)
-                  ptx::mma_tf32(d[hb], ptx::smem_desc_sw128(a_hi + ks * 32), ptx::smem_desc_sw128(b_addr[hb] + ks * 32), idh[hb],
-                                (kc == 0 && ks == 0) ? 0u : 1u);
-            } else {
+            for (int ks = 0; ks < 4; ++ks)
+              for (int hb = 0; hb < nh; ++hb)
+                ptx::mma_elect<false>(d[hb], a_hi_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idh[hb],
+                                      (kc == 0 && ks == 0) ? 0u : 1u);
+          } else {
 #pragma unroll
-              for (int ks = 0; ks < 4; ++ks)
-                for (int hb = 0; hb < nh; ++hb)
-                  ptx::mma_bf16(d[hb], ptx::smem_desc_sw128(a_lo + ks * 32), ptx::smem_desc_sw128(b_addr[hb] + ks * 32), idc[hb], 1u);
-            }
-            for (int hb = 0; hb < nh; ++hb) ptx::tc_commit(&bar->b_empty[slots[hb]]);
+            for (int ks = 0; ks < 4; ++ks)
+              for (int hb = 0; hb < nh; ++hb)
+                ptx::mma_elect<true>(d[hb], a_lo_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idc[hb], 1u);
           }
+          for (int hb = 0; hb < nh; ++hb) ptx::tc_commit_elect(&bar->b_empty[slots[hb]]);
           __syncwarp();
         }
-        if (lane == 0) {
-          ptx::tc_commit(&bar->a_empty[s]);
-          if (kc == p.KC - 1) {
-            ptx::tc_commit(&bar->tmem_full[g0 % 3]);
-            if (nh > 1) ptx::tc_commit(&bar->tmem_full[(g0 + 1) % 3]);
-          }
+        ptx::tc_commit_elect(&bar->a_empty[s]);
+        if (kc == p.KC - 1) {
+          ptx::tc_commit_elect(&bar->tmem_full[g0 % 3]);
+          if (nh > 1) ptx::tc_commit_elect(&bar->tmem_full[(g0 + 1) % 3]);
         }
         __syncwarp();
       }

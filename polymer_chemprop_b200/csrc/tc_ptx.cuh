@@ -12,6 +12,20 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// Warp index / warp-uniform values the compiler can PROVE uniform: a shuffle-broadcast from lane 0 (what CUTLASS's
+// canonical_warp_idx_sync does).  tcgen05.mma takes its descriptors in uniform registers; for operands whose uniformity
+// the compiler cannot prove it wraps every MMA in an ELECT / R2UR / BRA.U.ANY waterfall loop -- ~13 dependent
+// uniform-datapath instructions (~60 cycles) per MMA, as long as an M=128 x N=152 x K=8 MMA itself: measured, the
+// forward kernel was bound by that issue overhead, not by the tensor pipe or shared memory.
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+__device__ __forceinline__ uint32_t uniform_u32(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+// true in exactly one lane of a converged warp (elect.sync)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- mbarrier ------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -127,6 +141,56 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// MMA / commit issued from CONVERGENT code: all 32 lanes execute the statement, the election happens inside it
+// (elect.sync predicate on the instruction), so the operands live in warp-uniform control flow and the compiler can keep
+// them in uniform registers instead of wrapping each MMA in a waterfall loop.
+// Descriptors travel as (low word, constant high word): stepping along K inside a 128-byte swizzle row adds 2 to the low
+// word (32 bytes >> 4), one uniform add per operand and MMA instead of re-deriving the descriptor.
+template <bool BF16>
+__device__ __forceinline__ void mma_elect(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                          uint32_t accumulate) {
+  if (BF16) asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\telect.sync _|q, 0xffffffff;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                         "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+                         "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+                         ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+  else      asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\telect.sync _|q, 0xffffffff;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                         "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+                         "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}"
+                         ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_commit_elect(uint64_t* bar) {
+  asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+               "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// A-operand collector variants: COLL = 1 keeps the A tile in the tensor core's collector buffer after this MMA
+// (.collector::a::fill), COLL = 2 takes it from there instead of reading shared memory again and releases it
+// (.collector::a::lastuse); the MMA pair must be consecutive and use the same A descriptor.  COLL = 0: plain.
+template <int COLL, bool BF16>
+__device__ __forceinline__ void mma_coll(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  if (COLL == 1) {
+    if (BF16) asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::1.kind::f16.collector::a::fill [%0], %1, %2, %3, p;\n\t}"
+                           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+    else      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::1.kind::tf32.collector::a::fill [%0], %1, %2, %3, p;\n\t}"
+                           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+  } else if (COLL == 2) {
+    if (BF16) asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::1.kind::f16.collector::a::lastuse [%0], %1, %2, %3, p;\n\t}"
+                           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+    else      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::1.kind::tf32.collector::a::lastuse [%0], %1, %2, %3, p;\n\t}"
+                           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    if (BF16) asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+    else      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                           "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
 // same with bf16 inputs (kind::f16, K = 16 per instruction): the correction terms of the 3xTF32 scheme
 __device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                          uint32_t accumulate) {
@@ -192,6 +256,9 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;              // SWIZZLE_128B
   return d;
 }
+// the same descriptor as (low word, high word): see mma_elect
+__device__ __forceinline__ uint32_t desc_lo_sw128(uint32_t smem_addr) { return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16); }
+constexpr uint32_t kDescHiSw128 = (1024u >> 4) | (1u << 14) | (2u << 29);
 // Instruction descriptor, kind::tf32, fp32 accumulate, A and B K-major (cute UMMA::InstrDescriptor):
 // [4,6) c_format=1 (F32), [7,10) a_format=2 (TF32), [10,13) b_format=2, [15]/[16] majors = 0,
 // [17,23) N>>3, [24,29) M>>4.
