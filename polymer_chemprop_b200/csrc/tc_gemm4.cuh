@@ -109,6 +109,14 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
   for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
     const int slot = rit % T4_R_SLOTS;
     uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
+    if (WD_ABL & 64) {        // timing ablation: no epilogue work, only the slot protocol
+      if (EPI == E_RES_ACT) {
+        T2_WAIT(8, &bar->r_full[slot], (rit / T4_R_SLOTS) & 1);
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
+      }
+      continue;
+    }
     float v[32];
     const uint32_t ta = tmem_acc + ((uint32_t)(we * 32) << 16) + (uint32_t)c0;
     if (W - c0 >= 32) {
@@ -155,7 +163,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     // counters, profiles/r1_k_t4_role_wait_breakdown.log: the epilogue was 77 % busy and the MMA waited 20 % of the
     // kernel for a free accumulator).
     if (EPI == E_RES_ACT) {
-      ptx::fence_proxy_async_smem();          // generic accesses of the slot are ordered before the next TMA write
+      if (!(WD_ABL & 2048)) ptx::fence_proxy_async_smem();   // generic accesses of the slot are ordered before the next TMA write
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
     } else {
@@ -168,7 +176,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
       if (EPI != E_STORE) x = f4_act<ACT>(x);
       if (EPI != E_STORE && drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
       if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
-      if (in_c && row0 + we * 32 + rq + 4 * i < M) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
+      if (in_c && row0 + we * 32 + rq + 4 * i < M && !(WD_ABL & 4)) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
       if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
     }
   }
@@ -247,6 +255,11 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         T2_WAIT(0, &bar->raw_full[s], (it / T4_A_STAGES) & 1);
         uint8_t* st = ringA + s * T4_A_STAGE + po;
         uint8_t* x1 = ringA + s * T4_A_STAGE + TC_A_STAGE;
+        if (WD_ABL & 1024) {      // timing ablation: no transform work
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&bar->op_full[s]);
+          continue;
+        }
         float4 v[T4_XJ], u[T4_XJ];
 #pragma unroll
         for (int j = 0; j < T4_XJ; ++j) {
@@ -415,6 +428,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
               const int slot = u % nslots;
               T2_WAIT(3, &bar->b_empty[slot], ((u / nslots) & 1) ^ 1);
               const uint32_t bytes = (uint32_t)((hb ? W1 : W0) * 128);
+              if (WD_ABL & 4096) { ptx::mbar_arrive(&bar->b_full[slot]); continue; }     // timing ablation: no weight copies
               ptx::mbar_arrive_expect_tx(&bar->b_full[slot], bytes);
               ptx::bulk_g2s(ringB + (slot / nh) * b_stage + (hb ? W0 * 128 : 0), img + (hb ? W0 * 32 : 0), bytes,
                             &bar->b_full[slot]);
@@ -459,13 +473,15 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
               for (int hb = 0; hb < nh; ++hb)
-                ptx::mma_elect<false>(d[hb], a_hi_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idh[hb],
-                                      (kc == 0 && ks == 0) ? 0u : 1u);
+                if (!(WD_ABL & 128))
+                  ptx::mma_elect<false>(d[hb], a_hi_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idh[hb],
+                                        (kc == 0 && ks == 0) ? 0u : 1u);
           } else {
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
               for (int hb = 0; hb < nh; ++hb)
-                ptx::mma_elect<true>(d[hb], a_lo_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idc[hb], 1u);
+                if (!(WD_ABL & (128 | 512)))
+                  ptx::mma_elect<true>(d[hb], a_lo_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idc[hb], 1u);
           }
           for (int hb = 0; hb < nh; ++hb) ptx::tc_commit_elect(&bar->b_empty[slots[hb]]);
           __syncwarp();
