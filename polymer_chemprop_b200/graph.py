@@ -200,9 +200,38 @@ class BatchMolGraph:
     _TENSORS = ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "a2b", "b2a", "b2revb", "f_bonds_tail", "a_scope_array",
                 "dop_array")
 
+    # what DeviceGraph uploads for a batch that carries the bond-only tail (compact upload), in arena order
+    _UPLOAD = ("f_atoms", "f_bonds_tail", "w_atoms", "w_bonds", "a2b", "b2a", "b2revb", "a_scope_array", "dop_array")
+
+    def pack_arena(self, pin: bool = True) -> "BatchMolGraph":
+        """Lays everything the compact upload needs out in ONE host buffer (``_arena``; every array at a 256-byte
+        aligned offset, recorded in ``_arena_layout``) and turns the attributes into views of it, so that DeviceGraph
+        uploads the batch with a single copy.  Values and dtypes are unchanged."""
+        if self.f_bonds_tail is None or getattr(self, "_arena", None) is not None or self.f_atoms.device.type != "cpu":
+            return self
+        parts, off = {}, 0
+        for name in self._UPLOAD:
+            t = getattr(self, name).contiguous()
+            parts[name] = (off, t)
+            off += (t.numel() * t.element_size() + 255) // 256 * 256
+        arena = torch.empty(max(off, 256), dtype=torch.uint8)
+        if pin:
+            arena = arena.pin_memory()
+        layout = {}
+        for name, (o, t) in parts.items():
+            nb = t.numel() * t.element_size()
+            view = arena[o:o + nb].view(t.dtype).view(t.shape)
+            view.copy_(t)
+            setattr(self, name, view)
+            layout[name] = (o, nb)
+        self._arena, self._arena_layout = arena, layout
+        return self
+
     def pin_memory(self) -> "BatchMolGraph":
         """Page-locks the host tensors in place (what a DataLoader with pin_memory=True does to its batches), so
-        that DeviceGraph.prefetch can upload them asynchronously on a copy stream."""
+        that DeviceGraph.prefetch can upload them asynchronously on a copy stream; a batch that carries the
+        bond-only tail is packed into one pinned arena first (pack_arena)."""
+        self.pack_arena(pin=True)
         for name in self._TENSORS:
             t = getattr(self, name)
             if t is not None and t.device.type == "cpu" and not t.is_pinned():
@@ -228,4 +257,5 @@ class BatchMolGraph:
             setattr(self, name, t.to(device, non_blocking=True))
         if hasattr(self, "_wd_cache"):
             del self._wd_cache
+        self._arena = None
         return self

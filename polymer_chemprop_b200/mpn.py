@@ -49,7 +49,83 @@ class DeviceGraph:
         self._validate = validate
         self._checked = False
 
+    # Device buffers of a packed build, in arena order: (name, dtype, shape as a function of the sizes)
+    _PACKED_OUT = ("f_atoms", "f_bonds", "in_ptr", "in_idx", "out_idx", "src", "rev", "dst", "mol_of", "flags")
+
+    def _build_packed(self, mol_graph, device) -> bool:
+        """The upload of a batch that was packed into one pinned arena (BatchMolGraph.pack_arena): ONE host->device
+        copy, ONE device allocation for everything that is built (padded feature matrices, CSR arrays, flags), the
+        same two C calls.  Bit-identical to the tensor-by-tensor build (tests/test_gpu_parity.py); at batch 50 it takes
+        the host ~50 us instead of ~260 us (profiles/r2_c_b50_e2e_profile.log).  Tensor attributes (``f_atoms``,
+        ``in_ptr`` ...) are views created on first access."""
+        arena, lay = getattr(mol_graph, "_arena", None), getattr(mol_graph, "_arena_layout", None)
+        if arena is None or device.type != "cuda" or not arena.is_pinned():
+            return False
+        Fa, Fb = mol_graph.f_atoms.shape[1], mol_graph.f_bonds.shape[1]
+        Na, Nb, K = mol_graph.f_atoms.shape[0], mol_graph.f_bonds_tail.shape[0], mol_graph.a2b.shape[1]
+        G = mol_graph.dop_array.numel()
+        if mol_graph.f_bonds_tail.shape[1] != Fb - Fa or mol_graph.a_scope_array.numel() != 2 * G:
+            return False
+        self.device, self.atom_fdim, self.bond_fdim = device, Fa, Fb
+        self.n_atoms, self.n_bonds, self.n_mols = Na, Nb, G
+        self.compact_upload = True
+        d_in = arena.to(device, non_blocking=True)                       # the one upload
+        ld_a, ld_b = (Fa + 3) // 4 * 4, (Fb + 3) // 4 * 4
+        shapes = {"f_atoms": (torch.float32, (Na, ld_a)), "f_bonds": (torch.float32, (Nb, ld_b)),
+                  "in_ptr": (torch.int32, (Na + 1,)), "in_idx": (torch.int32, (max(Nb - 1, 1),)),
+                  "out_idx": (torch.int32, (max(Nb - 1, 1),)), "src": (torch.int32, (Nb,)), "rev": (torch.int32, (Nb,)),
+                  "dst": (torch.int32, (Nb,)), "mol_of": (torch.int32, (Na,)), "flags": (torch.int32, (4,))}
+        views, off = {}, 0
+        for name in self._PACKED_OUT:
+            dt, shp = shapes[name]
+            n = 4
+            for d in shp:
+                n *= d
+            views[name] = (1, off, n, dt, shp)
+            off += (n + 255) // 256 * 256
+        d_out = torch.empty(off, dtype=torch.uint8, device=device)
+        host_shapes = {"w_atoms": (torch.float32, (Na,)), "w_bonds": (torch.float32, (Nb,)),
+                       "a_start": (torch.int32, (G,)), "a_size": (torch.int32, (G,)), "dop": (torch.float32, (G,))}
+        so = lay["a_scope_array"][0]
+        in_off = {"w_atoms": lay["w_atoms"][0], "w_bonds": lay["w_bonds"][0], "a_start": so, "a_size": so + 4 * G,
+                  "dop": lay["dop_array"][0]}
+        for name, (dt, shp) in host_shapes.items():
+            views[name] = (0, in_off[name], 4 * shp[0], dt, shp)
+        self._arenas, self._views = (d_in, d_out), views
+        bi, bo = d_in.data_ptr(), d_out.data_ptr()
+        P = {name: (bo if v[0] else bi) + v[1] for name, v in views.items()}
+        L = _capi.lib()
+        stream = _capi.current_stream(device)
+        _capi.check(L.wd_expand_features(bi + lay["f_atoms"][0], bi + lay["f_bonds_tail"][0], bi + lay["b2a"][0], Na, Nb, Fa,
+                                         Fb - Fa, P["f_atoms"], ld_a, P["f_bonds"], ld_b, stream))
+        _capi.check(L.wd_csr_build(bi + lay["a2b"][0], Na, K, bi + lay["b2a"][0], bi + lay["b2revb"][0], Nb, P["a_start"],
+                                   P["a_size"], G, P["in_ptr"], P["in_idx"], P["out_idx"], P["src"], P["rev"], P["dst"],
+                                   P["mol_of"], P["flags"], stream))
+        self._dense_keepalive = self._int64_keepalive = None
+        self._host_keepalive = (arena,)                                 # pinned source of the in-flight copy
+        self.flags_host = _PINNED_FLAGS.pop() if _PINNED_FLAGS else torch.empty(4, dtype=torch.int32).pin_memory()
+        self.flags_host.copy_(self.flags, non_blocking=True)
+        self.build_stream = torch.cuda.current_stream(device)
+        self.ready = torch.cuda.Event()
+        self.ready.record(self.build_stream)
+        self.struct = _capi.WdGraph(Na, Nb, G, P["f_atoms"], P["f_bonds"], P["w_atoms"], P["w_bonds"], P["in_ptr"],
+                                    P["in_idx"], P["out_idx"], P["src"], P["rev"], P["dst"], P["mol_of"], P["a_start"],
+                                    P["a_size"], P["dop"], ld_a, ld_b)
+        return True
+
+    def __getattr__(self, name):
+        # tensor attributes of a packed build: views of the two arenas, made on first access
+        views = self.__dict__.get("_views")
+        if views is not None and name in views:
+            which, off, n, dt, shp = views[name]
+            t = self._arenas[which][off:off + n].view(dt).view(shp)
+            self.__dict__[name] = t
+            return t
+        raise AttributeError(name)
+
     def _build(self, mol_graph, device, non_blocking):
+        if self._build_packed(mol_graph, device):
+            return
         f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, a_scope, _b_scope, dop = \
             mol_graph.get_components(atom_messages=False)
         f32 = dict(device=device, dtype=torch.float32, non_blocking=non_blocking)
@@ -141,6 +217,8 @@ class DeviceGraph:
         return out
 
     def tensors(self):
+        if self.__dict__.get("_arenas") is not None:
+            return self._arenas
         return (self.f_atoms, self.f_bonds, self.w_atoms, self.w_bonds, self.a_start, self.dop, self.in_ptr,
                 self.in_idx, self.out_idx, self.src, self.rev, self.dst, self.mol_of, self.flags)
 

@@ -15,8 +15,10 @@ def num(r, name, default=0.0):
         return default
 
 
-ROLE = [("k_tc_gemm4", "gathered depth step"), ("k_tc_gemm3<1", "atom update (two K segments, bias+act)"),
-        ("k_tc_gemm3", "plain GEMM (input projection / dX)"), ("k_tc_dw5", "weight gradient"),
+ROLE = [("k_tc_gemm4<2", "gathered depth step"), ("k_tc_gemm4<0, 0", "input projection (3xTF32, plain operand)"),
+        ("k_tc_gemm4<0, 1", "atom update (3xTF32, two K segments, bias+act)"), ("k_tc_gemm4", "forward contraction"),
+        ("k_tc_gemm3<1", "atom update (two K segments, bias+act)"),
+        ("k_tc_gemm3", "plain GEMM (dX; input projection in tf32 mode)"), ("k_tc_dw5", "weight gradient"),
         ("k_message_grad", "message gradient"), ("k_aggregate", "aggregate / transpose-CSR scatter"),
         ("k_readout_grad", "readout backward"), ("k_readout", "readout"), ("k_expand_rows", "feature expansion (compact upload)"),
         ("k_reduce_partials", "split-K reduction"), ("k_colsum_partial", "bias-gradient column sums"), ("k_tc_pack_b", "weight packing")]

@@ -70,3 +70,24 @@ def test_bond_tail_only_when_prefix_property_holds():
     assert neg0[0].f_atoms[a, col] == 0.0
     neg0[0].f_bonds[0, col] = -0.0
     assert BatchMolGraph(neg0).f_bonds_tail is None
+
+
+def test_pack_arena_keeps_values_dtypes_and_shapes():
+    """pack_arena lays the upload set out in one host buffer (256-byte aligned offsets) and re-points the attributes
+    at views of it; nothing else changes (CPU here: the arena is not pinned)."""
+    import torch
+    from polymer_chemprop_b200 import BatchMolGraph, synth
+    graphs = synth.make_graphs("copolymer", 9, 3, dense_features=True)
+    a, b = BatchMolGraph(graphs), BatchMolGraph(graphs).pack_arena(pin=False)
+    assert b._arena.dtype == torch.uint8 and set(b._arena_layout) == set(BatchMolGraph._UPLOAD)
+    end = 0
+    for name in BatchMolGraph._UPLOAD:
+        x, y = getattr(a, name), getattr(b, name)
+        off, nb = b._arena_layout[name]
+        assert off % 256 == 0 and off >= end and nb == x.numel() * x.element_size()
+        end = off + nb
+        assert x.dtype == y.dtype and x.shape == y.shape and torch.equal(x, y), name
+        assert y.data_ptr() == b._arena.data_ptr() + off
+    assert end <= b._arena.numel()
+    assert [torch.equal(u, v) for u, v in zip(a.get_components()[:7], b.get_components()[:7])] == [True] * 7
+    assert b.pack_arena(pin=False) is b and b.fresh_view()._arena is b._arena          # idempotent, shared by views

@@ -12,7 +12,7 @@ import torch
 import _golden
 import _util
 from oracle import mpn_oracle
-from polymer_chemprop_b200 import BatchMolGraph, DeviceGraph, _capi, synth
+from polymer_chemprop_b200 import MPN, BatchMolGraph, DeviceGraph, _capi, synth
 
 pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda", 0)
@@ -82,6 +82,38 @@ def test_compact_upload_rebuilds_features_bit_exactly():
     pre.use_on(torch.cuda.current_stream(DEV))
     pre.check()
     assert pre.compact_upload and torch.equal(pre.f_bonds, full.f_bonds) and torch.equal(pre.f_atoms, full.f_atoms)
+
+
+def test_packed_upload_is_bit_identical_to_the_tensor_by_tensor_build():
+    """BatchMolGraph.pin_memory packs the upload set into ONE pinned arena; DeviceGraph then uploads with a single copy
+    and builds everything into a single device allocation.  Same bytes in every array, same encoder output and gradients
+    (bitwise), on the current stream and on a copy stream."""
+    graphs = synth.make_graphs("copolymer", 120, 5, dense_features=True, random_edge_weights=True) + [synth.empty_graph()] + \
+        synth.make_graphs("qm9", 40, 6)
+    plain = BatchMolGraph(graphs)
+    packed = BatchMolGraph(graphs).pin_memory()
+    assert packed._arena is not None and packed._arena.is_pinned() and getattr(plain, "_arena", None) is None
+    for name in BatchMolGraph._UPLOAD:
+        assert torch.equal(getattr(packed, name), getattr(plain, name)), name
+    ref = DeviceGraph(plain, DEV)
+    ref.check()
+    side = torch.cuda.Stream(device=DEV)
+    for dg in (DeviceGraph(packed.fresh_view(), DEV), DeviceGraph.prefetch(packed.fresh_view(), DEV, side)):
+        assert dg.__dict__.get("_arenas") is not None and dg.compact_upload
+        dg.use_on(torch.cuda.current_stream(DEV))
+        dg.check()
+        assert (dg.violations, dg.max_in_degree, dg.rev_adjacent) == (ref.violations, ref.max_in_degree, ref.rev_adjacent)
+        for name in ("f_atoms", "f_bonds", "w_atoms", "w_bonds", "in_ptr", "in_idx", "out_idx", "src", "rev", "dst", "mol_of",
+                     "a_start", "a_size", "dop"):
+            a, b = getattr(dg, name), getattr(ref, name)
+            assert a.shape == b.shape and a.dtype == b.dtype and torch.equal(a.view(torch.int32), b.view(torch.int32)), name
+    torch.manual_seed(2)
+    model = MPN(_util.make_args(hidden_size=64, depth=3, wd_math_mode="tf32x3"), atom_fdim=plain.atom_fdim,
+                bond_fdim=plain.bond_fdim).to(DEV)
+    d_out = torch.randn(len(graphs), 64)
+    out_a, grads_a = _util.run_fwd_bwd(model, plain, d_out)
+    out_b, grads_b = _util.run_fwd_bwd(model, packed.fresh_view(), d_out)
+    assert torch.equal(out_a, out_b) and all(torch.equal(grads_a[k], grads_b[k]) for k in grads_a)
 
 
 @pytest.mark.parametrize("name", _golden.NAMES)
