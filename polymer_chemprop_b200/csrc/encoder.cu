@@ -379,9 +379,39 @@ int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const floa
   return WD_OK;
 }
 
+// A second branch of a captured pass (small batches, GraphRun below): work that is off the critical path -- the weight
+// gradients, the bias column sums, the weight packing -- is captured on a side stream, so the executable graph may run it
+// next to the dA -> dM -> dS -> dA chain instead of inside it.  At batch 50 no kernel fills the GPU for long (8-24 us
+// each), the chain is latency-bound, and four of its sixteen links are weight-gradient kernels nothing downstream waits
+// for until the final reduction.  Without a side stream (eager launches, large batches) every call is a no-op and the
+// work stays on the main stream, in the same order.
+struct SideBranch {
+  cudaStream_t main = nullptr, side = nullptr;
+  cudaEvent_t ev[8] = {};
+  int next = 0;
+  bool on() const { return side != nullptr; }
+  cudaStream_t stream() const { return side ? side : main; }
+  int fork() {          // the side branch waits for everything launched on the main stream so far
+    if (!side) return WD_OK;
+    cudaEvent_t e = ev[next++ & 7];
+    WD_CUDA_OK(cudaEventRecord(e, main));
+    WD_CUDA_OK(cudaStreamWaitEvent(side, e, 0));
+    return WD_OK;
+  }
+  int join() {          // the main stream waits for everything launched on the side branch so far
+    if (!side) return WD_OK;
+    cudaEvent_t e = ev[next++ & 7];
+    WD_CUDA_OK(cudaEventRecord(e, side));
+    WD_CUDA_OK(cudaStreamWaitEvent(main, e, 0));
+    return WD_OK;
+  }
+};
+
 template <int ACT>
 int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* ws, const float* d_out,
-                  const WdGrads& gr, cudaStream_t s) {
+                  const WdGrads& gr, cudaStream_t s, SideBranch sd = SideBranch{}) {
+  sd.main = s;
+  const cudaStream_t s2 = sd.stream();     // where the off-chain work goes: the side branch when there is one
   Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
   const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim, Fo = Fa + h;
   bind_packed(c, L, ws);
@@ -390,7 +420,8 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     TcPacker pk;                       // one launch for the two transposed backward weights
     if (c.depth > 1) pk.add(w.W_h, h, B_KN, L.pWhT);
     pk.add(w.W_o + Fa, Fo, B_KN, L.pWoT);
-    WD_TRY(pk.run(s));
+    WD_TRY(sd.fork());                 // (side branch: next to the readout gradient, joined before the first dX)
+    WD_TRY(pk.run(s2));
   }
   const int64_t Na = g.n_atoms, Nb = g.n_bonds;
   const int d = c.depth;
@@ -411,9 +442,11 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     WD_LAUNCH((k_readout_grad<ACT, false>), (unsigned)ceil_div(Na, rpb), 256, 0, s, d_out, h, H, ld, g.w_atoms, g.mol_of,
               L.p(ws, L.mscale), dZo, Na, make_dropout(c, c.depth), rpb); }
   // dZo (114 MB at B=4096) has just been written and fits L2: its three readers run back to back, smallest first
+  if (L.tc) WD_TRY(sd.join());         // the packed weights are ready for the main stream
+  WD_TRY(sd.fork());                   // dZo is ready for the side branch
   {  // db_o = colsum(dZo)
     ProfScope ps(WD_PROF_DW);
-    WD_TRY(colsum(s, dZo, ld, Pcol, gr.db_o, Na, h, red));
+    WD_TRY(colsum(s2, dZo, ld, Pcol, gr.db_o, Na, h, red));
   }
   // dA_d = dZo * W_o[:, F_a:]
   AOperand a_zo{dZo, nullptr, nullptr, nullptr, ld, 0, 0};
@@ -423,7 +456,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     ProfScope ps(WD_PROF_DW);
     const int Z = L.Zo;
     AOperand y{g.f_atoms, A_d, nullptr, nullptr, g.ld_atoms ? g.ld_atoms : Fa, ld, Fa};
-    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s, dZo, ld, y, Fa, h, Po, Na, h, Z)));
+    WD_TRY((dw_partial<A_CONCAT, ACT, false>(c, s2, dZo, ld, y, Fa, h, Po, Na, h, Z)));
     WD_TRY(red.add(Po, gr.dW_o, (int64_t)h * Fo, Z));
   }
 
@@ -440,6 +473,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     const bool pre = (t == 1);
     // dZ_t = dM_t * act'(M_t), dI += dZ_t ; dM_t = w_b dA[dst b] - dS[rev b] (symmetrised if undirected)
     const SignBits sg = sign_bits(L, ws, Nb, t, L.pWh);
+    if (d - 1 - t >= 2) WD_TRY(sd.join());   // this step overwrites the dZ buffer the weight gradient of two steps ago reads
     if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI, make_dropout(c, t), sg))); sum = dZ; }
     else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI, make_dropout(c, t), sg))); sum = dI; }
     // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
@@ -448,6 +482,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     const bool have_S = L.tc;   // forward kept S_t (tensor-core path)
     if (c.undirected && !have_S) {
       float* U = L.p(ws, L.U);
+      WD_TRY(sd.join());               // the previous step's weight gradient (side branch) still reads U
       if (pre) WD_LAUNCH((k_symmetrize<ACT, true>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
       else     WD_LAUNCH((k_symmetrize<ACT, false>), grid1d(Nb * nc4), 256, 0, s, M_prev, ld, g.rev, U, Nb, nc4);
       u = U;
@@ -455,12 +490,13 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     }
     AOperand y{A_t, u, g.src, g.rev, ld, ld, 0};
     float* Pt = Ph + (int64_t)(d - 1 - t) * Zh * h * h;
+    WD_TRY(sd.fork());                 // dZ_t (and the symmetrised U) are ready for the side branch
     { ProfScope ps(WD_PROF_DW);
     if (have_S) {   // the forward pass left S_t in the workspace: a plain TMA-fed contraction
       AOperand ys{L.p(ws, L.S) + (int64_t)(t - 1) * L.szB, nullptr, nullptr, nullptr, ld, 0, 0};
-      WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s, dZ, ld, ys, h, 0, Pt, Nb, h, Zh)));
-    } else if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh)));
-    else      WD_TRY((dw_partial<A_GATHER_DIFF, ACT, false>(c, s, dZ, ld, y, h, 0, Pt, Nb, h, Zh))); }
+      WD_TRY((dw_partial<A_PLAIN, ACT, false>(c, s2, dZ, ld, ys, h, 0, Pt, Nb, h, Zh)));
+    } else if (upre) WD_TRY((dw_partial<A_GATHER_DIFF, ACT, true>(c, s2, dZ, ld, y, h, 0, Pt, Nb, h, Zh)));
+    else      WD_TRY((dw_partial<A_GATHER_DIFF, ACT, false>(c, s2, dZ, ld, y, h, 0, Pt, Nb, h, Zh))); }
     // dS = dZ_t * W_h ; dA[a] = sum over out-edges of a of dS  (transpose-CSR, no atomics)
     AOperand a_z{dZ, nullptr, nullptr, nullptr, ld, 0, 0};
     { ProfScope ps(WD_PROF_DX);
@@ -486,6 +522,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     WD_TRY(red.add(Pi, gr.dW_i, (int64_t)h * Fb, Z));
     if (c.bias && gr.db_i) WD_TRY(colsum(s, dI, ld, Pcol + 2 * pcol, gr.db_i, Nb, h, red));
   }
+  WD_TRY(sd.join());                   // every partial is written before the one reduction launch
   return red.run(s);
 }
 
@@ -513,6 +550,26 @@ struct GraphRun {
       st[dev] = nullptr;
     }
     return st[dev];
+  }
+  // the side branch of a captured pass (SideBranch above): a second private stream and the events that tie it in
+  SideBranch side_branch() const {
+    SideBranch sb;
+    if (!active) return sb;
+    thread_local cudaStream_t st[64] = {};
+    thread_local cudaEvent_t ev[64][8] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return sb; }
+    if (st[dev] == nullptr) {
+      if (cudaStreamCreateWithFlags(&st[dev], cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); st[dev] = nullptr; return sb; }
+      for (int i = 0; i < 8; ++i)
+        if (cudaEventCreateWithFlags(&ev[dev][i], cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); return sb; }
+    }
+    for (int i = 0; i < 8; ++i) {
+      if (ev[dev][i] == nullptr) return sb;
+      sb.ev[i] = ev[dev][i];
+    }
+    sb.side = st[dev];
+    return sb;
   }
   using Key = std::array<int64_t, 14>;
   static std::mutex& mu() { static std::mutex m; return m; }
@@ -562,7 +619,7 @@ struct GraphRun {
       }
     }
     if (exec == nullptr) {
-      if (cc.size() >= 64) { for (auto& kv : cc) cudaGraphExecDestroy(kv.second); cc.clear(); }
+      if (cc.size() >= 512) { for (auto& kv : cc) cudaGraphExecDestroy(kv.second); cc.clear(); }
       const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
       if (ei != cudaSuccess) { cudaGraphDestroy(graph); return fail(WD_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ei)); }
       cc[key] = exec;
@@ -651,7 +708,8 @@ extern "C" int wd_encoder_backward(const WdGraph* graph, const WdWeights* weight
   int rc = WD_OK;
   {
     GraphRun gr((cudaStream_t)stream, *cfg, *graph);
-    WD_DISPATCH_ACT(cfg->activation, rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, gr.stream()));
+    const SideBranch sb = (cfg->flags & WD_FLAG_NO_SIDE_BRANCH) ? SideBranch{} : gr.side_branch();
+    WD_DISPATCH_ACT(cfg->activation, rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, gr.stream(), sb));
     rc = gr.finish(rc, 2, *cfg, *graph);
   }
   if (rc == kRetryEagerly) WD_DISPATCH_ACT(cfg->activation, rc = backward_impl<ACT>(*graph, *weights, *cfg, workspace, d_out, *grads, (cudaStream_t)stream));

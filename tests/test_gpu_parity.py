@@ -293,22 +293,25 @@ def test_edge_shapes_match_oracle(case, mode, out_tol, grad_tol):
         assert _golden.rel_err(grads[k], ref) <= grad_tol, k
 
 
-@pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
-def test_small_batches_run_as_one_cuda_graph_per_pass_with_the_same_bits(mode, monkeypatch):
+@pytest.mark.parametrize("mode,depth,bias", [("fp32", 3, False), ("tf32x3", 3, False), ("tf32x3", 5, True), ("tf32x3", 2, True)])
+def test_small_batches_run_as_one_cuda_graph_per_pass_with_the_same_bits(mode, depth, bias, monkeypatch):
     """Small batches (the reference's default is 50 graphs, chemprop/args.py:95): the library captures each pass into a
     CUDA graph and re-parameterises ONE executable graph per pass for every new batch (cudaGraphExecUpdate: new
     pointers, sizes, grids and tensor maps).  Same kernels, same order => bitwise the same results as the plain launches
-    (WD_GRAPH=0 -> WdConfig.flags & WD_FLAG_NO_GRAPH), for batches of different sizes in a row."""
+    (WD_GRAPH=0 -> WdConfig.flags & WD_FLAG_NO_GRAPH), for batches of different sizes in a row.  In the captured backward
+    pass the weight-gradient kernels sit on a parallel branch of the graph (csrc/encoder.cu: SideBranch; depth 5 exercises
+    the join that protects the alternating dZ buffers): still the same bits, also against WD_SIDE_BRANCH=0."""
     batches = [BatchMolGraph(synth.make_graphs("copolymer", n, 200 + n, random_edge_weights=True)) for n in (50, 37, 64)]
     torch.manual_seed(2)
-    model = _util.MPN(_util.make_args(hidden_size=300, depth=3, wd_math_mode=mode), atom_fdim=batches[0].atom_fdim,
-                      bond_fdim=batches[0].bond_fdim).to(DEV)
+    model = _util.MPN(_util.make_args(hidden_size=300, depth=depth, bias=bias, wd_math_mode=mode),
+                      atom_fdim=batches[0].atom_fdim, bond_fdim=batches[0].bond_fdim).to(DEV)
     for p in model.parameters():
         if p.requires_grad and p.dim() == 2:
             torch.nn.init.xavier_normal_(p)
     res = {}
-    for flag in ("1", "0"):
-        monkeypatch.setenv("WD_GRAPH", flag)
+    for flag in ("1", "0", "no_side"):
+        monkeypatch.setenv("WD_GRAPH", "0" if flag == "0" else "1")
+        monkeypatch.setenv("WD_SIDE_BRANCH", "0" if flag == "no_side" else "1")
         g0, b0 = _capi.graph_stats()
         outs = []
         for bmg in batches:
@@ -317,13 +320,14 @@ def test_small_batches_run_as_one_cuda_graph_per_pass_with_the_same_bits(mode, m
             with torch.no_grad():
                 outs.append((model([bmg.fresh_view()]).cpu(), {}))
         g1, b1 = _capi.graph_stats()
-        if flag == "1":
+        if flag != "0":
             assert g1 - g0 == 9                      # forward, backward, infer for each of the three batches
             assert b1 - b0 <= 3                      # at most one executable graph per pass; the rest were updates
         else:
             assert g1 == g0
         res[flag] = outs
-    for (o1, gr1), (o0, gr0) in zip(res["1"], res["0"]):
-        assert torch.equal(o1, o0)
-        for k in gr1:
-            assert torch.equal(gr1[k], gr0[k]), k
+    for other in ("0", "no_side"):
+        for (o1, gr1), (o0, gr0) in zip(res["1"], res[other]):
+            assert torch.equal(o1, o0)
+            for k in gr1:
+                assert torch.equal(gr1[k], gr0[k]), (other, k)
