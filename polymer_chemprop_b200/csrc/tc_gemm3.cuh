@@ -58,6 +58,7 @@ __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane,
                                             int64_t row0, int64_t M, int col0, int N, int cmax, const float* bias,
                                             float* C, int ldc, const Dropout& drop, const SignBits& sign) {
   uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
+  const int rows_ok = (int)min((int64_t)32, M - (row0 + we * 32));         // rows of this warp inside the matrix (may be <= 0)
   for (int c0 = 0; c0 < BN; c0 += 32, ++rit) {
     const int slot = rit % T2_R_SLOTS;
     uint8_t* sl = rring + slot * T2_R_SLOT_BYTES + (we * 32) * T2_R_ROW;     // this warp's 32 rows
@@ -79,6 +80,7 @@ __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane,
     const int colb = col0 + c0 + pc * 4;
     const int nval = (c0 + pc * 4 < BN) ? max(0, min(4, N - colb)) : 0;      // live columns of this piece
     const bool in_c = colb < cmax && c0 + pc * 4 < BN;
+    const bool edge = c0 + 32 > BN || col0 + c0 + 32 > N;                   // warp-uniform: some lane has masked columns
     float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
     if (bias != nullptr) {
       if (nval > 0) bv.x = __ldg(bias + colb);
@@ -92,11 +94,12 @@ __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane,
     float* cp = C + (row0 + we * 32 + rq) * ldc + colb;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
+      float4 x = xv[i];
+      if (bias != nullptr) x = make_float4(x.x + bv.x, x.y + bv.y, x.z + bv.z, x.w + bv.w);       // warp-uniform
       if (EPI != E_STORE) x = f4_act<ACT>(x);
       if (EPI != E_STORE && drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
-      if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
-      const bool ok = in_c && row0 + we * 32 + rq + 4 * i < M && !(WD_ABL & 4);
+      if (edge && nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
+      const bool ok = in_c && rq + 4 * i < rows_ok && !(WD_ABL & 4);
       if (ok) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
       if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
     }

@@ -106,6 +106,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
                                             const float* bias, float* C, int ldc, long long* tacc,
                                             const Dropout& drop, const SignBits& sign, int sign_tile) {
   uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
+  const int rows_ok = (int)min((int64_t)32, M - (row0 + we * 32));        // rows of this warp inside the matrix (may be <= 0)
   for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
     const int slot = rit % T4_R_SLOTS;
     uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
@@ -144,6 +145,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     const int colb = col0 + c0 + pc * 4;
     const int nval = (c0 + pc * 4 < W) ? max(0, min(4, N - colb)) : 0;
     const bool in_c = colb < cmax && c0 + pc * 4 < W;
+    const bool edge = c0 + 32 > W || col0 + c0 + 32 > N;                  // warp-uniform: some lane has masked columns
     float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
     if (bias != nullptr) {
       if (nval > 0) bv.x = __ldg(bias + colb);
@@ -172,11 +174,12 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     float* cp = C + (row0 + we * 32 + rq) * ldc + colb;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float4 x = make_float4(xv[i].x + bv.x, xv[i].y + bv.y, xv[i].z + bv.z, xv[i].w + bv.w);
+      float4 x = xv[i];
+      if (bias != nullptr) x = make_float4(x.x + bv.x, x.y + bv.y, x.z + bv.z, x.w + bv.w);       // warp-uniform
       if (EPI != E_STORE) x = f4_act<ACT>(x);
       if (EPI != E_STORE && drop.thresh != 0u) x = dropout4(x, drop, (row0 + we * 32 + rq + 4 * i) * ldc + colb);
-      if (nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
-      if (in_c && row0 + we * 32 + rq + 4 * i < M && !(WD_ABL & 4)) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
+      if (edge && nval < 4) { x.w = 0.f; if (nval < 3) x.z = 0.f; if (nval < 2) x.y = 0.f; if (nval < 1) x.x = 0.f; }
+      if (in_c && rq + 4 * i < rows_ok && !(WD_ABL & 4)) *reinterpret_cast<float4*>(cp + (int64_t)(4 * i) * ldc) = x;
       if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
     }
   }
