@@ -62,9 +62,24 @@ inline bool pdl_enabled() {
   return g_pdl != 0;
 }
 
+// Launches that do not carry the programmatic-serialisation attribute: the attribute describes ONE primary kernel per
+// secondary.  A kernel with two predecessors -- everything on the side branch of a captured pass (its own predecessor
+// there + the main-stream kernel it was forked after), and the first main-stream kernel after a join -- is therefore
+// launched with ordinary (full) dependencies.  No measurable cost at batch 50 (0.191 vs 0.192 ms per step);
+// scripts/side_branch_stress.py passes either way (WD_SIDE_PLAIN=0 keeps the attribute, for A/B runs).
+struct PdlGuard {
+  cudaStream_t plain_stream = nullptr;   // every launch on this stream is a plain one
+  bool plain_once = false;               // the next launch (on any stream) is a plain one
+};
+inline PdlGuard& pdl_guard() { thread_local PdlGuard g; return g; }
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
                                  Args&&... args) {
+  PdlGuard& pg = pdl_guard();
+  static const bool guard_on = [] { const char* e = getenv("WD_SIDE_PLAIN"); return !(e && atoi(e) == 0); }();
+  const bool plain = guard_on && (pg.plain_once || (pg.plain_stream != nullptr && s == pg.plain_stream));
+  if (s != pg.plain_stream) pg.plain_once = false;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -74,7 +89,7 @@ inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, 
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = (pdl_enabled() && !g_prof_on) ? 1 : 0;
+  cfg.numAttrs = (pdl_enabled() && !g_prof_on && !plain) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 

@@ -403,6 +403,7 @@ struct SideBranch {
     cudaEvent_t e = ev[next++ & 7];
     WD_CUDA_OK(cudaEventRecord(e, side));
     WD_CUDA_OK(cudaStreamWaitEvent(main, e, 0));
+    pdl_guard().plain_once = true;     // the next main-stream kernel has two predecessors: full edges (common.cuh)
     return WD_OK;
   }
 };
@@ -412,6 +413,10 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
                   const WdGrads& gr, cudaStream_t s, SideBranch sd = SideBranch{}) {
   sd.main = s;
   const cudaStream_t s2 = sd.stream();     // where the off-chain work goes: the side branch when there is one
+  struct PlainSide {                       // launches on the side branch carry no programmatic-launch attribute (common.cuh)
+    explicit PlainSide(cudaStream_t st) { pdl_guard().plain_stream = st; }
+    ~PlainSide() { pdl_guard().plain_stream = nullptr; pdl_guard().plain_once = false; }
+  } plain_side(sd.side);
   Layout L = make_layout(c, g.n_atoms, g.n_bonds, g.n_mols);
   const int h = c.hidden_size, ld = L.ldh, nc4 = ld / 4, Fa = c.atom_fdim, Fb = c.bond_fdim, Fo = Fa + h;
   bind_packed(c, L, ws);

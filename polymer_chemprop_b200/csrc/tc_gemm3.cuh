@@ -25,7 +25,13 @@ constexpr int T2_R_BYTES = T2_R_SLOTS * T2_R_SLOT_BYTES;
 
 constexpr int T3_STAGES = 4;
 constexpr int T3_PROD_WARP = 5;
-constexpr int T3_THREADS = 32 * 6;
+// optional second epilogue group (warps 6-9, TMEM lane quarter = warp % 4; see tc_gemm4.cuh): measured no gain for this
+// kernel (dX 117.9 us either way), so the default stays one group
+#ifndef WD_T3_EPI_GROUPS
+#define WD_T3_EPI_GROUPS 1
+#endif
+constexpr int T3_EPI_GROUPS = WD_T3_EPI_GROUPS, T3_EPI2_W0 = 6;
+constexpr int T3_THREADS = 32 * (6 + (T3_EPI_GROUPS - 1) * 4);
 
 struct T3Barriers {
   uint64_t full[T3_STAGES], empty[T3_STAGES];
@@ -56,11 +62,13 @@ inline int t3_smem_bytes(int BN) {
 template <int EPI, int ACT>
 __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, uint32_t& rit, int BN,
                                             int64_t row0, int64_t M, int col0, int N, int cmax, const float* bias,
-                                            float* C, int ldc, const Dropout& drop, const SignBits& sign) {
+                                            float* C, int ldc, const Dropout& drop, const SignBits& sign, int grp) {
   uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
   const int rows_ok = (int)min((int64_t)32, M - (row0 + we * 32));         // rows of this warp inside the matrix (may be <= 0)
+  const uint32_t rit0 = rit;
   for (int c0 = 0; c0 < BN; c0 += 32, ++rit) {
-    const int slot = rit % T2_R_SLOTS;
+    if (T3_EPI_GROUPS > 1 && (int)(rit & 1u) != grp) continue;             // the other group's chunk
+    const int slot = T3_EPI_GROUPS > 1 ? grp : (int)(rit % T2_R_SLOTS);     // staging only: one slot per group
     uint8_t* sl = rring + slot * T2_R_SLOT_BYTES + (we * 32) * T2_R_ROW;     // this warp's 32 rows
     float v[32];
     const uint32_t ta = tmem_acc + ((uint32_t)(we * 32) << 16) + (uint32_t)c0;
@@ -105,7 +113,9 @@ __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane,
     }
     __syncwarp();
   }
-  if (sign.p != nullptr) sign_flush(sign, sw, col0 / BN, row0 + we * 32, M, lane >> 3, lane & 7, (BN + 31) >> 5);
+  // lane pc holds the word of chunk pc: with two groups only if this group wrote it
+  if (sign.p != nullptr && (T3_EPI_GROUPS == 1 || (int)((rit0 + (uint32_t)(lane & 7)) & 1u) == grp))
+    sign_flush(sign, sw, col0 / BN, row0 + we * 32, M, lane >> 3, lane & 7, (BN + 31) >> 5);
 }
 
 template <int EPI, int ACT>
@@ -124,7 +134,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < T3_STAGES; ++s) { ptx::mbar_init(&bar->full[s], 1); ptx::mbar_init(&bar->empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { ptx::mbar_init(&bar->tmem_full[a], 1); ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(&bar->tmem_full[a], 1); ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS * T3_EPI_GROUPS); }
     ptx::fence_barrier_init();
     ptx::tma_prefetch_desc(&p.ma[0]);
   }
@@ -172,17 +182,18 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
         __syncwarp();
       }
     }
-  } else if (warp < T2_EPI_WARPS) {
-    // ================= epilogue =================
+  } else if (warp < T2_EPI_WARPS || warp >= T3_EPI2_W0) {
+    // ================= epilogue (warps 0-3, and 6-9 as the second group) =================
     uint32_t tl = 0, rit = 0;
+    const int grp = warp >= T3_EPI2_W0 ? 1 : 0, wq = warp & 3;
     for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x, ++tl) {
       const int acc = tl & 1;
       const int64_t row0 = (tile / p.n_tiles) * TC_BM;
       const int col0 = (int)(tile % p.n_tiles) * p.BN;
       T2_WAIT(7, &bar->tmem_full[acc], (tl >> 1) & 1);
       ptx::tc_fence_after();
-      t3_epilogue<EPI, ACT>(tmem_base + acc * 256, warp, lane, rring, rit, p.BN, row0, p.M, col0, p.N, p.ldc, p.bias,
-                            p.C, p.ldc, p.drop, p.sign);
+      t3_epilogue<EPI, ACT>(tmem_base + acc * 256, wq, lane, rring, rit, p.BN, row0, p.M, col0, p.N, p.ldc, p.bias,
+                            p.C, p.ldc, p.drop, p.sign, grp);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);

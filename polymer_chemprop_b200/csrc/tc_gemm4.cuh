@@ -49,8 +49,18 @@ namespace wd {
 constexpr int T4_MMA_WARP = 4, T4_B_WARP = 5, T4_R_WARP = 6, T4_LOAD_W0 = 7, T4_LOAD_WARPS = 4, T4_XFORM_W0 = 11,
               T4_XFORM_WARPS = WD_T4_XFORM_WARPS;
 constexpr int T4_XR = 4 * T4_XFORM_WARPS, T4_XJ = TC_BM / T4_XR;   // transform: rows per pass / passes per chunk
-constexpr int T4_THREADS = 32 * (T4_XFORM_W0 + T4_XFORM_WARPS);
-constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_B_SLOTS = 2 * T4_B_STAGES, T4_R_SLOTS = 3;
+// Epilogue groups: 1 = warps 0-3 (the default); 2 = a second group of four warps after the transform warps (TMEM lane
+// quarter = warp % 4 in both), the groups taking alternate 32-column chunks.  EXPERIMENTAL, compile-time only: it measured
+// 1.8 % faster per step (depth-step contraction 328 -> 309 us, profiles/r2_fwd_abl.log section G) but
+// scripts/side_branch_stress.py found one step in ~60 whose results differ from the one-group kernel's -- a race between
+// the groups that is not yet located -- so it is NOT enabled.
+#ifndef WD_T4_EPI_GROUPS
+#define WD_T4_EPI_GROUPS 1
+#endif
+constexpr int T4_EPI_GROUPS = WD_T4_EPI_GROUPS, T4_EPI2_W0 = T4_XFORM_W0 + T4_XFORM_WARPS;
+constexpr int T4_THREADS = 32 * (T4_EPI2_W0 + (T4_EPI_GROUPS - 1) * 4);
+constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_R_SLOTS = 3;
+constexpr int T4_B_SLOTS = 4 * T4_B_STAGES;      // weight-ring units: 2 per stage; a CTA pair keeps half of each unit, so twice as many fit
 constexpr int T4_X1_ROWS = 132, T4_X1_LEAD = 2;   // TMA box of the subtrahend rows: [row0 - 2, row0 + 130)
 constexpr int T4_X1_STAGE = 17 * 1024;            // >= T4_X1_ROWS * 128 bytes, keeps the stages 1024-byte aligned
 constexpr int T4_A_STAGE = TC_A_STAGE + T4_X1_STAGE;   // minuend rows / a_hi (128 x 128 bytes) + subtrahend rows / a_lo
@@ -90,6 +100,7 @@ struct T4Params {
   int x1_tma;           // GATHER: 1: i1(r) == ((r-1)^1)+1 for every r >= 1 (adjacent reverse pairs): X1 rows arrive by TMA
   int a_tma;            // PLAIN: 1: rows are 16-byte aligned and arrive by TMA; 0: 4-byte cp.async copies
   int split;            // 1: 3xTF32 (hi / lo operand images, three MMAs per K step); 0: single-pass TF32
+  CUtensorMap mb[2];    // CTA pair: the packed weight images as one [rows, 32] matrix, box = (W0 / 2, W1 / 2) rows, no swizzle
 };
 
 inline int t4_smem_bytes(int BN) {
@@ -104,11 +115,15 @@ template <int EPI, int ACT>
 __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T4Barriers* bar,
                                             uint32_t& rit, int W, int64_t row0, int64_t M, int col0, int N, int cmax,
                                             const float* bias, float* C, int ldc, long long* tacc,
-                                            const Dropout& drop, const SignBits& sign, int sign_tile) {
+                                            const Dropout& drop, const SignBits& sign, int sign_tile, int grp) {
   uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
   const int rows_ok = (int)min((int64_t)32, M - (row0 + we * 32));        // rows of this warp inside the matrix (may be <= 0)
+  const uint32_t rit0 = rit;
   for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
-    const int slot = rit % T4_R_SLOTS;
+    if (T4_EPI_GROUPS > 1 && (int)(rit & 1u) != grp) continue;            // the other group's chunk
+    // the residual's ring slot (handed over chunk by chunk through r_full / r_empty); without a residual the slot is
+    // only staging and nothing orders the two groups, so each keeps to a slot of its own
+    const int slot = (EPI == E_RES_ACT || T4_EPI_GROUPS == 1) ? (int)(rit % T4_R_SLOTS) : grp;
     uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
     if (WD_ABL & 64) {        // timing ablation: no epilogue work, only the slot protocol
       if (EPI == E_RES_ACT) {
@@ -183,21 +198,39 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
       if (sign.p != nullptr) sign_collect(sw[i], x, rq, pc, c0 >> 5);   // warp-uniform branch
     }
   }
-  if (sign.p != nullptr) sign_flush(sign, sw, sign_tile, row0 + we * 32, M, lane >> 3, lane & 7, (W + 31) >> 5);
+  // lane pc holds the word of chunk pc: with two groups only if this group wrote it
+  if (sign.p != nullptr && (T4_EPI_GROUPS == 1 || (int)((rit0 + (uint32_t)(lane & 7)) & 1u) == grp))
+    sign_flush(sign, sw, sign_tile, row0 + we * 32, M, lane >> 3, lane & 7, (W + 31) >> 5);
 }
 
-template <int AMODE, int EPI, int ACT, bool PREACT>
-__global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constant__ T4Params p) {
+// PAIR: the kernel runs as clusters of two CTAs on the two SMs of a TPC (cta_group::2).  A pair owns 256 rows: the even
+// CTA (the leader) rows [0, 128), the odd one rows [128, 256); each loads, transforms and writes out its own rows exactly
+// as a single CTA does.  What changes is the weight operand and the MMA: each CTA fetches only HALF of the rows of every
+// weight unit (N / 2) -- the L2 -> SM weight stream, the shared-memory writes and the ring footprint per SM halve, so the
+// ring holds four K chunks' worth instead of two -- and the leader issues ONE M = 256 tcgen05.mma.cta_group::2 per K
+// step for both SMs, each tensor core reading both halves.  Signals that feed the issuing warp (operand ready,
+// accumulator free) go to the LEADER's barriers from both CTAs; the weight boxes arrive by cta_group::2 TMA loads that
+// count their bytes on the leader's barrier; completion (stage free, accumulator full) is committed to both CTAs at once.
+// Why: profiles/r2_fwd_abl.log -- in the 3xTF32 mode the weight stream (two packed images per K chunk, 778 KB from L2
+// per 128-row tile) costs 72 us of the 324 us depth-step contraction and the kernel moves ~3.4 MB through shared memory
+// per tile.
+template <int AMODE, int EPI, int ACT, bool PREACT, bool PAIR>
+__device__ __forceinline__ void t4_body(const T4Params& p) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   constexpr bool GATHER = AMODE == A_GATHER_DIFF;
+  constexpr int TILE_ROWS = PAIR ? 2 * TC_BM : TC_BM;                  // rows of one scheduled tile (a pair's or a CTA's)
+  const uint32_t rank = PAIR ? ptx::cluster_ctarank() : 0u;            // 0: leader (issues the MMAs)
+  const int64_t t_first = PAIR ? (blockIdx.x >> 1) : blockIdx.x, t_step = PAIR ? (gridDim.x >> 1) : gridDim.x;
+  const int64_t rank_rows = (int64_t)rank * TC_BM;
   static_assert(GATHER || !PREACT, "PREACT belongs to the gathered operand");
   extern __shared__ uint8_t smem_raw[];
   const int warp = ptx::uniform_warp_idx(), lane = threadIdx.x & 31;   // provably warp-uniform: see tc_ptx.cuh
   const uint32_t base = ptx::smem_u32(smem_raw);
   uint8_t* ringA = smem_raw + (((base + 1023u) & ~1023u) - base);      // 1024-aligned
-  const int b_stage = p.BN * 128;
+  const int b_stage = PAIR ? p.BN * 64 : p.BN * 128;                   // one chunk image (PAIR: this CTA's half of its rows)
+  constexpr int B_STAGES = PAIR ? 2 * T4_B_STAGES : T4_B_STAGES;       // same ring bytes either way
   uint8_t* ringB = ringA + T4_A_STAGES * T4_A_STAGE;
-  uint8_t* rring = ringB + T4_B_STAGES * b_stage;
+  uint8_t* rring = ringB + T4_B_STAGES * (p.BN * 128);
   T4Barriers* bar = reinterpret_cast<T4Barriers*>(rring + T4_R_SLOTS * T4_R_SLOT);
   long long tacc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   const long long t_start = clock64();
@@ -208,38 +241,46 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     const uint32_t raw_count = GATHER ? 32 * T4_LOAD_WARPS + (p.x1_tma ? 1 : 0) : (p.a_tma ? 1 : 32 * T4_LOAD_WARPS);
     for (int s = 0; s < T4_A_STAGES; ++s) {
       ptx::mbar_init(&bar->raw_full[s], raw_count);
-      ptx::mbar_init(&bar->op_full[s], T4_XFORM_WARPS);
+      ptx::mbar_init(&bar->op_full[s], T4_XFORM_WARPS * (PAIR ? 2 : 1));     // PAIR: both CTAs report to the leader
       ptx::mbar_init(&bar->a_empty[s], 1);
     }
     for (int s = 0; s < T4_B_SLOTS; ++s) { ptx::mbar_init(&bar->b_full[s], 1); ptx::mbar_init(&bar->b_empty[s], 1); }
     for (int s = 0; s < T4_R_SLOTS; ++s) { ptx::mbar_init(&bar->r_full[s], 1); ptx::mbar_init(&bar->r_empty[s], T2_EPI_WARPS); }
-    for (int a = 0; a < 3; ++a) { ptx::mbar_init(&bar->tmem_full[a], 1); ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS); }
+    for (int a = 0; a < 3; ++a) {
+      ptx::mbar_init(&bar->tmem_full[a], 1);
+      ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS * T4_EPI_GROUPS * (PAIR ? 2 : 1));
+    }
     ptx::fence_barrier_init();
     if (EPI == E_RES_ACT) ptx::tma_prefetch_desc(&p.mr);
     if (GATHER && p.x1_tma) ptx::tma_prefetch_desc(&p.mx1);
     if (!GATHER && p.a_tma) ptx::tma_prefetch_desc(&p.ma[0]);
   }
-  if (warp == T4_MMA_WARP) ptx::tmem_alloc(&bar->tmem_base, TC_TMEM_COLS);
+  if (warp == T4_MMA_WARP) {
+    if (PAIR) ptx::tmem_alloc_pair(&bar->tmem_base, TC_TMEM_COLS);
+    else ptx::tmem_alloc(&bar->tmem_base, TC_TMEM_COLS);
+  }
   ptx::tc_fence_before();
   __syncthreads();
+  if (PAIR) ptx::cluster_sync();       // the partner's barriers are initialised before anything arrives on them
   ptx::tc_fence_after();
   const uint32_t tmem_base = bar->tmem_base;
-  const int64_t total = ceil_div(p.M, TC_BM) * p.n_tiles;
+  const int64_t total = ceil_div(p.M, TILE_ROWS) * p.n_tiles;
   const int W0 = min(p.BN, T4_HALF), W1 = p.BN - W0;                  // accumulator halves of a column tile
   // The weight ring holds T4_B_STAGES chunk images [BN x 128 bytes]; it is filled and drained in UNITS of one
   // accumulator half of one image (hi, then lo when split), each unit with its own full / empty barrier: unit u
   // lives in slot u % (2 nh) = (stage, half).
-  const int nh = W1 > 0 ? 2 : 1, parts = p.split ? 2 : 1, nslots = T4_B_STAGES * nh;
+  const int nh = W1 > 0 ? 2 : 1, parts = p.split ? 2 : 1, nslots = B_STAGES * nh;
+  const int h1_off = PAIR ? W0 * 64 : W0 * 128;                        // where the second half's unit starts inside a stage
 
-  if (warp >= T4_XFORM_W0) {
+  if (warp >= T4_XFORM_W0 && warp < T4_EPI2_W0) {
     // ================= transform, in place: X0 <- tf32(a), X1 part <- tf32(a - tf32(a)),  a = X0 - act?(X1) =================
     // (Fetching the subtrahend rows with plain loads into registers instead was measured SLOWER: the proxy fence
     //  below is a MEMBAR that also waits for the thread's outstanding global loads, i.e. for the prefetch.)
     const int t = threadIdx.x - 32 * T4_XFORM_W0, c = t & 7, rb = t >> 3;
     const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));   // rows rb + T4_XR j share rb & 7
     uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+    for (int64_t tile = t_first; tile < total; tile += t_step) {
+      const int64_t row0 = (tile / p.n_tiles) * TILE_ROWS + rank_rows;
       const bool keep = GATHER && p.S != nullptr && (tile % p.n_tiles) == 0;
       uint32_t uoff[T4_XJ];                       // where this thread's subtrahend pieces sit in the X1 part of a stage
 #pragma unroll
@@ -260,7 +301,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         uint8_t* x1 = ringA + s * T4_A_STAGE + TC_A_STAGE;
         if (WD_ABL & 1024) {      // timing ablation: no transform work
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&bar->op_full[s]);
+          if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&bar->op_full[s]); else ptx::mbar_arrive(&bar->op_full[s]); }
           continue;
         }
         float4 v[T4_XJ], u[T4_XJ];
@@ -290,7 +331,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         }
         ptx::fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&bar->op_full[s]);
+        if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&bar->op_full[s]); else ptx::mbar_arrive(&bar->op_full[s]); }
         const int kcol = kc * TC_BK + c * 4;                             // S goes out after the hand-off to the MMA
         if (keep && kcol < p.lds) {
 #pragma unroll
@@ -301,7 +342,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
         }
       }
     }
-  } else if (warp >= T4_LOAD_W0) {
+  } else if (warp >= T4_LOAD_W0 && warp < T4_XFORM_W0) {
     const int t = threadIdx.x - 32 * T4_LOAD_W0;
     const uint32_t ring_u32 = ptx::smem_u32(ringA);
     if (GATHER) {
@@ -309,8 +350,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
       const int c = t & 7, rb = t >> 3;
       const uint32_t po = (uint32_t)(rb * 128 + ((c ^ (rb & 7)) << 4));
       uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+      for (int64_t tile = t_first; tile < total; tile += t_step) {
+        const int64_t row0 = (tile / p.n_tiles) * TILE_ROWS + rank_rows;
         const float* s0[8];
         const float* s1[8];
         uint32_t okmask = 0;
@@ -364,8 +405,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
       // ================= plain operand: one TMA box (128 rows x 32 columns, raw fp32) per K chunk =================
       if (t == 0) {
         uint32_t it = 0;
-        for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-          const int row0 = (int)((tile / p.n_tiles) * TC_BM);
+        for (int64_t tile = t_first; tile < total; tile += t_step) {
+          const int row0 = (int)((tile / p.n_tiles) * TILE_ROWS + rank_rows);
           for (int kc = 0; kc < p.KC; ++kc, ++it) {
             const int s = it % T4_A_STAGES;
             T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
@@ -380,8 +421,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
       // ================= plain operand, rows only 4-byte aligned (dense 133 / 147-float feature rows) =================
       const int col = t & 31, r4 = t >> 5;
       uint32_t it = 0;
-      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+      for (int64_t tile = t_first; tile < total; tile += t_step) {
+        const int64_t row0 = (tile / p.n_tiles) * TILE_ROWS + rank_rows;
         for (int kc = 0; kc < p.KC; ++kc, ++it) {
           const int s = it % T4_A_STAGES;
           T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
@@ -406,8 +447,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     // ================= residual loader: TMA boxes of 128 rows x 32 columns, ahead of the epilogue =================
     if (EPI == E_RES_ACT && lane == 0) {
       uint32_t rit = 0;
-      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int row0 = (int)((tile / p.n_tiles) * TC_BM);
+      for (int64_t tile = t_first; tile < total; tile += t_step) {
+        const int row0 = (int)((tile / p.n_tiles) * TILE_ROWS + rank_rows);
         const int col0 = (int)(tile % p.n_tiles) * p.BN;
         for (int c0 = 0; c0 < p.BN; c0 += 32, ++rit) {
           // the halves are walked in order: columns [0, W0) then [W0, BN); W0 is a multiple of 32 whenever W1 > 0
@@ -422,7 +463,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     // ================= weight loader: one bulk copy per unit (K chunk, hi | lo image, accumulator half) =================
     if (lane == 0) {
       uint32_t u = 0;
-      for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      for (int64_t tile = t_first; tile < total; tile += t_step) {
         const int nt = (int)(tile % p.n_tiles);
         for (int kc = 0; kc < p.KC; ++kc) {
           for (int part = 0; part < parts; ++part) {
@@ -431,9 +472,17 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
               const int slot = u % nslots;
               T2_WAIT(3, &bar->b_empty[slot], ((u / nslots) & 1) ^ 1);
               const uint32_t bytes = (uint32_t)((hb ? W1 : W0) * 128);
+              if (PAIR) {
+                // this CTA's half of the unit's rows; both boxes count on the leader's barrier, which the leader arms
+                const int wh = (hb ? W1 : W0) / 2;
+                const int row = (int)((((int64_t)nt * p.KC + kc) * parts + part) * p.BN) + (hb ? W0 : 0) + (int)rank * wh;
+                if (rank == 0) ptx::mbar_arrive_expect_tx(&bar->b_full[slot], bytes);
+                ptx::tma_load_2d_pair(ringB + (slot / nh) * b_stage + (hb ? h1_off : 0), &p.mb[hb], 0, row, &bar->b_full[slot]);
+                continue;
+              }
               if (WD_ABL & 4096) { ptx::mbar_arrive(&bar->b_full[slot]); continue; }     // timing ablation: no weight copies
               ptx::mbar_arrive_expect_tx(&bar->b_full[slot], bytes);
-              ptx::bulk_g2s(ringB + (slot / nh) * b_stage + (hb ? W0 * 128 : 0), img + (hb ? W0 * 32 : 0), bytes,
+              ptx::bulk_g2s(ringB + (slot / nh) * b_stage + (hb ? h1_off : 0), img + (hb ? W0 * 32 : 0), bytes,
                             &bar->b_full[slot]);
             }
           }
@@ -445,9 +494,10 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
     uint32_t it = 0, g = 0, u = 0;                                      // g: accumulator halves issued so far; u: weight units
     const uint32_t ringA_u = ptx::uniform_u32(ptx::smem_u32(ringA)), ringB_u = ptx::uniform_u32(ptx::smem_u32(ringB));
     const uint32_t tmem_u = ptx::uniform_u32(tmem_base);
-    const uint32_t idh[2] = {ptx::idesc_tf32(128, W0), ptx::idesc_tf32(128, W1 > 0 ? W1 : 16)};
-    const uint32_t idc[2] = {ptx::idesc_bf16(128, W0), ptx::idesc_bf16(128, W1 > 0 ? W1 : 16)};
-    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    constexpr int MM = PAIR ? 256 : 128;                                // rows of one MMA (PAIR: both CTAs' tiles)
+    const uint32_t idh[2] = {ptx::idesc_tf32(MM, W0), ptx::idesc_tf32(MM, W1 > 0 ? W1 : 16)};
+    const uint32_t idc[2] = {ptx::idesc_bf16(MM, W0), ptx::idesc_bf16(MM, W1 > 0 ? W1 : 16)};
+    for (int64_t tile = (PAIR && rank != 0) ? total : t_first; tile < total; tile += t_step) {     // PAIR: the leader issues
       const uint32_t g0 = g;
       g += nh;
       for (int kc = 0; kc < p.KC; ++kc, ++it) {
@@ -467,7 +517,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
             T2_WAIT(6, &bar->b_full[slot], (u / nslots) & 1);
             const uint32_t gb = g0 + hb;
             if (kc == 0 && part == 0) T2_WAIT(4, &bar->tmem_empty[gb % 3], ((gb / 3) & 1) ^ 1);
-            b_addr[hb] = ptx::desc_lo_sw128(ringB_u + (slot / nh) * b_stage + (hb ? W0 * 128 : 0));
+            b_addr[hb] = ptx::desc_lo_sw128(ringB_u + (slot / nh) * b_stage + (hb ? h1_off : 0));
             d[hb] = tmem_u + (gb % 3) * T4_HALF;
           }
           ptx::tc_fence_after();
@@ -476,43 +526,59 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
               for (int hb = 0; hb < nh; ++hb)
-                if (!(WD_ABL & 128))
+                if (WD_ABL & 128) {
+                } else if (PAIR) {
+                  ptx::mma_elect_pair<false>(d[hb], a_hi_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idh[hb],
+                                             (kc == 0 && ks == 0) ? 0u : 1u);
+                } else {
                   ptx::mma_elect<false>(d[hb], a_hi_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idh[hb],
                                         (kc == 0 && ks == 0) ? 0u : 1u);
+                }
           } else {
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
               for (int hb = 0; hb < nh; ++hb)
-                if (!(WD_ABL & (128 | 512)))
+                if (WD_ABL & (128 | 512)) {
+                } else if (PAIR) {
+                  ptx::mma_elect_pair<true>(d[hb], a_lo_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idc[hb], 1u);
+                } else {
                   ptx::mma_elect<true>(d[hb], a_lo_lo + 2 * ks, b_addr[hb] + 2 * ks, ptx::kDescHiSw128, idc[hb], 1u);
+                }
           }
-          for (int hb = 0; hb < nh; ++hb) ptx::tc_commit_elect(&bar->b_empty[slots[hb]]);
+          // (PAIR: every completion below is committed to the barrier at the same offset in BOTH CTAs)
+          for (int hb = 0; hb < nh; ++hb) { if (PAIR) ptx::tc_commit_elect_pair(&bar->b_empty[slots[hb]]); else ptx::tc_commit_elect(&bar->b_empty[slots[hb]]); }
           __syncwarp();
         }
-        ptx::tc_commit_elect(&bar->a_empty[s]);
+        if (PAIR) ptx::tc_commit_elect_pair(&bar->a_empty[s]); else ptx::tc_commit_elect(&bar->a_empty[s]);
         if (kc == p.KC - 1) {
-          ptx::tc_commit_elect(&bar->tmem_full[g0 % 3]);
-          if (nh > 1) ptx::tc_commit_elect(&bar->tmem_full[(g0 + 1) % 3]);
+          if (PAIR) {
+            ptx::tc_commit_elect_pair(&bar->tmem_full[g0 % 3]);
+            if (nh > 1) ptx::tc_commit_elect_pair(&bar->tmem_full[(g0 + 1) % 3]);
+          } else {
+            ptx::tc_commit_elect(&bar->tmem_full[g0 % 3]);
+            if (nh > 1) ptx::tc_commit_elect(&bar->tmem_full[(g0 + 1) % 3]);
+          }
         }
         __syncwarp();
       }
     }
   } else {
-    // ================= epilogue (warps 0-3) =================
+    // ================= epilogue (warps 0-3; with two groups also the four warps after the transform warps) =================
     uint32_t g = 0, rit = 0;
-    for (int64_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      const int64_t row0 = (tile / p.n_tiles) * TC_BM;
+    const int grp = warp >= T4_EPI2_W0 ? 1 : 0, wq = warp & 3;             // TMEM lane quarter / rows of the tile: warp % 4
+    for (int64_t tile = t_first; tile < total; tile += t_step) {
+      const int64_t row0 = (tile / p.n_tiles) * TILE_ROWS + rank_rows;
       const int col0 = (int)(tile % p.n_tiles) * p.BN;
       for (int hb = 0; hb < nh; ++hb, ++g) {
         const int buf = g % 3;
         T2_WAIT(7, &bar->tmem_full[buf], (g / 3) & 1);
         ptx::tc_fence_after();
-        t4_epilogue<EPI, ACT>(tmem_base + buf * T4_HALF, warp, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
+        t4_epilogue<EPI, ACT>(tmem_base + buf * T4_HALF, wq, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
                               col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop, p.sign,
-                              (int)(tile % p.n_tiles) * p.sign.tpn + hb);
+                              (int)(tile % p.n_tiles) * p.sign.tpn + hb, grp);
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[buf]);
+        if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&bar->tmem_empty[buf]); else ptx::mbar_arrive(&bar->tmem_empty[buf]); }
       }
     }
   }
@@ -527,10 +593,22 @@ __global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constan
 #endif
   ptx::tc_fence_before();
   __syncthreads();
+  if (PAIR) ptx::cluster_sync();       // the partner's shared memory and barriers stay alive until both CTAs are done
   if (warp == T4_MMA_WARP) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
+    if (PAIR) ptx::tmem_dealloc_pair(tmem_base, TC_TMEM_COLS);
+    else ptx::tmem_dealloc(tmem_base, TC_TMEM_COLS);
   }
+}
+
+template <int AMODE, int EPI, int ACT, bool PREACT>
+__global__ void __launch_bounds__(T4_THREADS, 1) k_tc_gemm4(const __grid_constant__ T4Params p) {
+  t4_body<AMODE, EPI, ACT, PREACT, false>(p);
+}
+// the CTA-pair form: clusters of two CTAs, grid size even
+template <int AMODE, int EPI, int ACT, bool PREACT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T4_THREADS, 1) k_tc_gemm4_pair(const __grid_constant__ T4Params p) {
+  t4_body<AMODE, EPI, ACT, PREACT, true>(p);
 }
 
 }  // namespace wd

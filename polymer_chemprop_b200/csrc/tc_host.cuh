@@ -113,6 +113,25 @@ int tc_gemm4(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   p.N = B.N; p.BN = B.BN; p.n_tiles = B.n_tiles;
   const int smem = t4_smem_bytes(B.BN);
   if (smem > TC_SMEM_LIMIT) return fail(WD_ERR_UNSUPPORTED, "tcgen05 tile does not fit shared memory");
+  // CTA pairs (cta_group::2, tc_gemm4.cuh: t4_body<..., PAIR>): OPT-IN (WD_T4_PAIR=1).  Parity-green and bitwise equal to
+  // the single-CTA kernel, but measured 1-12 % SLOWER on B200 at both h = 300 and h = 2400 (profiles/r2_fwd_abl.log,
+  // section F): halving the weight stream per SM buys less than the lock-step of two SMs costs.
+  const char* pair_env = getenv("WD_T4_PAIR");           // read per call: the A/B test flips it
+  const bool pair_on = pair_env && atoi(pair_env) == 1;
+  const int W0 = std::min(B.BN, T4_HALF), W1 = B.BN - W0;
+  if (pair_on && ceil_div(M, TC_BM) >= 2 * kNumSMs && W0 % 16 == 0 && W1 % 16 == 0) {
+    const int64_t img_rows = (int64_t)B.n_tiles * B.KC * B.parts * B.BN;
+    rc = tma_make_2d(&p.mb[0], B.img, img_rows, 32, 32, W0 / 2, TMA_NO_SWIZZLE, /*round_tf32=*/false);
+    if (rc == WD_OK && W1 > 0) rc = tma_make_2d(&p.mb[1], B.img, img_rows, 32, 32, W1 / 2, TMA_NO_SWIZZLE, /*round_tf32=*/false);
+    if (rc != WD_OK) return rc;
+    auto kern = k_tc_gemm4_pair<GATHER ? A_GATHER_DIFF : A_PLAIN, EPI, ACT2, GATHER && PREACT>;
+    rc = tc_set_smem(kern, smem);
+    if (rc != WD_OK) return rc;
+    const int64_t tiles = ceil_div(M, 2 * TC_BM) * B.n_tiles;
+    const unsigned grid = 2u * (unsigned)std::min<int64_t>(tiles, kNumSMs / 2);
+    WD_LAUNCH(kern, grid, T4_THREADS, smem, s, p);
+    return WD_OK;
+  }
   auto kern = k_tc_gemm4<GATHER ? A_GATHER_DIFF : A_PLAIN, EPI, ACT2, GATHER && PREACT>;
   rc = tc_set_smem(kern, smem);
   if (rc != WD_OK) return rc;

@@ -163,6 +163,50 @@ __device__ __forceinline__ void tc_commit_elect(uint64_t* bar) {
                "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// ---- CTA pair (cta_group::2): two CTAs of a cluster on the two SMs of a TPC run ONE M = 256 MMA -------------------------
+// Rows [0, 128) of A and of the accumulator live in the even CTA (the leader, which issues), rows [128, 256) in the odd
+// one; each CTA holds HALF of the B rows (N / 2) at the same shared-memory offset, and each SM's tensor core reads both
+// halves.  A shared::cluster address with bit 24 cleared names the same offset in the leader's shared memory.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrival on the barrier at this offset in the LEADER's shared memory (from either CTA of the pair)
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_result, uint32_t cols) {  // whole warp, same warp in both CTAs
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t cols) {  // whole warp, same warp in both CTAs
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+template <bool BF16>
+__device__ __forceinline__ void mma_elect_pair(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                               uint32_t accumulate) {
+  if (BF16) asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\telect.sync _|q, 0xffffffff;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                         "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+                         "@q tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n\t}"
+                         ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+  else      asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\telect.sync _|q, 0xffffffff;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+                         "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+                         "@q tcgen05.mma.cta_group::2.kind::tf32 [%0], da, db, %4, p;\n\t}"
+                         ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+// completion of the pair's MMAs so far -> one arrival on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tc_commit_elect_pair(uint64_t* bar) {
+  asm volatile("{\n\t.reg .pred q;\n\t.reg .b16 m;\n\telect.sync _|q, 0xffffffff;\n\tmov.b16 m, 3;\n\t"
+               "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}"
+               ::"r"(smem_u32(bar)) : "memory");
+}
+
 // A-operand collector variants: COLL = 1 keeps the A tile in the tensor core's collector buffer after this MMA
 // (.collector::a::fill), COLL = 2 takes it from there instead of reading shared memory again and releases it
 // (.collector::a::lastuse); the MMA pair must be consecutive and use the same A descriptor.  COLL = 0: plain.

@@ -253,3 +253,28 @@ def test_sign_bits_give_the_same_gradients_as_the_stored_activations_bitwise(hid
     assert len(res["1"][1]) >= 3
     for k in res["1"][1]:
         assert torch.equal(res["1"][1][k], res["0"][1][k]), k
+
+
+@pytest.mark.parametrize("mode", ["tf32x3", "tf32"])
+def test_cta_pair_kernel_gives_the_same_bits_as_the_single_cta_kernel(mode, monkeypatch):
+    """WD_T4_PAIR=1 runs the forward contractions as clusters of two CTAs (tcgen05.mma.cta_group::2: one M = 256 MMA
+    per pair, each CTA holding half of every weight unit; csrc/tc_gemm4.cuh).  Same products accumulated in the same
+    order per output element => bitwise the same output and gradients as the default single-CTA kernel.  (Opt-in: it
+    measured slower, profiles/r2_fwd_abl.log section F.)  The batch has >= 2 * 148 row tiles, the kernel's threshold,
+    and an odd number of 128-row tiles, so one pair's second CTA has no rows at all."""
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 700, 17, random_edge_weights=True))
+    n_tiles = (bmg.n_bonds + 127) // 128
+    assert n_tiles >= 296
+    torch.manual_seed(4)
+    model = _util.MPN(_util.make_args(hidden_size=300, depth=3, wd_math_mode=mode), atom_fdim=bmg.atom_fdim,
+                      bond_fdim=bmg.bond_fdim).to(DEV)
+    d_out = torch.randn(len(bmg.a_scope), 300, generator=torch.Generator().manual_seed(5))
+    res = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("WD_T4_PAIR", flag)
+        monkeypatch.setenv("WD_GRAPH", "0")
+        res[flag] = _util.run_fwd_bwd(model, bmg, d_out)
+    (o0, g0), (o1, g1) = res["0"], res["1"]
+    assert torch.isfinite(o1).all() and torch.equal(o0, o1)
+    for k in g0:
+        assert torch.equal(g0[k], g1[k]), k
