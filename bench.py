@@ -428,9 +428,12 @@ def run_train_step(a, mpn, params, store, rng, batch, dev, world, copy_stream, s
         one()
     sync_all()
     k = max(3, min(a.steps, 20))
+    walls = []
     t0 = time.perf_counter()
     for _ in range(k):
+        ts = time.perf_counter()
         loss = one()
+        walls.append(1e3 * (time.perf_counter() - ts))     # host time to ENQUEUE the step (nothing is waited for)
     float(loss.detach())                          # the step's loss reaches the host
     sync_all()
     te = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
@@ -439,6 +442,7 @@ def run_train_step(a, mpn, params, store, rng, batch, dev, world, copy_stream, s
     if reducer is not None:
         reducer.detach()
     return {"value": world * batch / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()), "steps": k,
+            "host_enqueue_ms_median": float(np.median(walls)), "host_enqueue_ms": [round(w, 3) for w in walls],
             "what": "store batch -> MPN -> fused FFN(300, 1) + masked MSE (wd_head_*) -> backward -> all-reduce -> FlatAdam, "
                     "wall clock; the step's loss is read on the host at the end of the timed run"}
 
