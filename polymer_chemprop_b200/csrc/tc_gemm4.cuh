@@ -37,7 +37,8 @@
 // not by the weight traffic.  No extra HBM pass: the correction image of A is written over the subtrahend part of
 // the SAME smem stage (after a named barrier among the transform warps when that part holds the shared TMA box);
 // the weight ring streams two images per chunk from L2.
-//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 operand loaders, 11-14 transform.
+//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 operand loaders, 11-14 transform,
+//   15-18 second epilogue group.
 #pragma once
 #include "tc_gemm3.cuh"
 
@@ -49,13 +50,14 @@ namespace wd {
 constexpr int T4_MMA_WARP = 4, T4_B_WARP = 5, T4_R_WARP = 6, T4_LOAD_W0 = 7, T4_LOAD_WARPS = 4, T4_XFORM_W0 = 11,
               T4_XFORM_WARPS = WD_T4_XFORM_WARPS;
 constexpr int T4_XR = 4 * T4_XFORM_WARPS, T4_XJ = TC_BM / T4_XR;   // transform: rows per pass / passes per chunk
-// Epilogue groups: 1 = warps 0-3 (the default); 2 = a second group of four warps after the transform warps (TMEM lane
-// quarter = warp % 4 in both), the groups taking alternate 32-column chunks.  EXPERIMENTAL, compile-time only: it measured
-// 1.8 % faster per step (depth-step contraction 328 -> 309 us, profiles/r2_fwd_abl.log section G) but
-// scripts/side_branch_stress.py found one step in ~60 whose results differ from the one-group kernel's -- a race between
-// the groups that is not yet located -- so it is NOT enabled.
+// Epilogue groups: 2 (the default) = warps 0-3 plus a second group of four warps after the transform warps (TMEM lane
+// quarter = warp % 4 in both), the groups taking alternate 32-column chunks; 1 = warps 0-3 only.  Measured
+// (profiles/r2_fwd_abl.log section G): depth-step contraction 328 -> 309 us, forward pass 1258 -> 1206 us, step 2.916 ->
+// 2.864 ms.  The first version shared the residual ring's "box landed" barriers between the groups and failed the
+// bitwise stress test once in ~60 steps (a parity wait that skips every second phase, see t4_rfull); with a barrier set
+// per group it passes (6 x 240 steps).
 #ifndef WD_T4_EPI_GROUPS
-#define WD_T4_EPI_GROUPS 1
+#define WD_T4_EPI_GROUPS 2
 #endif
 constexpr int T4_EPI_GROUPS = WD_T4_EPI_GROUPS, T4_EPI2_W0 = T4_XFORM_W0 + T4_XFORM_WARPS;
 constexpr int T4_THREADS = 32 * (T4_EPI2_W0 + (T4_EPI_GROUPS - 1) * 4);
@@ -71,7 +73,7 @@ static_assert(T4_LOAD_WARPS * 32 == TC_BM && (T4_XFORM_WARPS == 4 || T4_XFORM_WA
 struct T4Barriers {
   uint64_t raw_full[T4_A_STAGES], op_full[T4_A_STAGES], a_empty[T4_A_STAGES];
   uint64_t b_full[T4_B_SLOTS], b_empty[T4_B_SLOTS];
-  uint64_t r_full[T4_R_SLOTS], r_empty[T4_R_SLOTS];
+  uint64_t r_full[T4_R_SLOTS * 2], r_empty[T4_R_SLOTS];    // r_full: one set per epilogue group (t4_rfull below)
   uint64_t tmem_full[3], tmem_empty[3];
   uint32_t tmem_base;
 };
@@ -107,6 +109,18 @@ inline int t4_smem_bytes(int BN) {
   return 1024 + T4_A_STAGES * T4_A_STAGE + T4_B_STAGES * BN * 128 + T4_R_SLOTS * T4_R_SLOT + (int)sizeof(T4Barriers) + 64;
 }
 
+// Which "residual box has landed" barrier belongs to chunk `rit` (ring slot rit % 3), and the parity of its phase.  With
+// two epilogue groups the uses of a slot alternate between the groups (chunks c, c + 3, c + 6 ...); a parity wait is only
+// meaningful for a waiter that consumes EVERY phase, so each group has its own barrier per slot (the loader arms the
+// one of the group that will read the box): a group's chunks in one slot are 6 apart.  (With a shared barrier a box of
+// the other group that lands late lets the wait for c + 6 succeed on the phase of c: one corrupted step in ~60.)
+__device__ __forceinline__ int t4_rfull(uint32_t rit) {
+  return (int)(rit % T4_R_SLOTS) + (T4_EPI_GROUPS > 1 ? (int)(rit & 1u) * T4_R_SLOTS : 0);
+}
+__device__ __forceinline__ uint32_t t4_rfull_parity(uint32_t rit) {
+  return (rit / (T4_R_SLOTS * T4_EPI_GROUPS)) & 1u;
+}
+
 // Epilogue of one accumulator half (128 rows x W columns), 32 columns at a time: the row-owning thread adds its
 // accumulator row to the residual chunk in the (swizzled) ring slot (EPI == E_RES_ACT; otherwise the slot is only the
 // transpose staging of this warp's 32 rows), then the warp writes the 32 rows out with 16-byte stores (8 lanes per
@@ -127,7 +141,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     uint8_t* sl = rring + slot * T4_R_SLOT + (we * 32) * 128;               // this warp's 32 rows (row & 7 == lane & 7)
     if (WD_ABL & 64) {        // timing ablation: no epilogue work, only the slot protocol
       if (EPI == E_RES_ACT) {
-        T2_WAIT(8, &bar->r_full[slot], (rit / T4_R_SLOTS) & 1);
+        T2_WAIT(8, &bar->r_full[t4_rfull(rit)], t4_rfull_parity(rit));
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
       }
@@ -142,7 +156,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
 #pragma unroll
       for (int j = 16; j < 32; ++j) v[j] = 0.f;
     }
-    if (EPI == E_RES_ACT) T2_WAIT(8, &bar->r_full[slot], (rit / T4_R_SLOTS) & 1);
+    if (EPI == E_RES_ACT) T2_WAIT(8, &bar->r_full[t4_rfull(rit)], t4_rfull_parity(rit));
     ptx::tmem_ld_wait();
     uint8_t* myrow = sl + lane * 128;
 #pragma unroll
@@ -245,7 +259,11 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
       ptx::mbar_init(&bar->a_empty[s], 1);
     }
     for (int s = 0; s < T4_B_SLOTS; ++s) { ptx::mbar_init(&bar->b_full[s], 1); ptx::mbar_init(&bar->b_empty[s], 1); }
-    for (int s = 0; s < T4_R_SLOTS; ++s) { ptx::mbar_init(&bar->r_full[s], 1); ptx::mbar_init(&bar->r_empty[s], T2_EPI_WARPS); }
+    for (int s = 0; s < T4_R_SLOTS; ++s) {
+      ptx::mbar_init(&bar->r_full[s], 1);
+      ptx::mbar_init(&bar->r_full[s + T4_R_SLOTS], 1);
+      ptx::mbar_init(&bar->r_empty[s], T2_EPI_WARPS);
+    }
     for (int a = 0; a < 3; ++a) {
       ptx::mbar_init(&bar->tmem_full[a], 1);
       ptx::mbar_init(&bar->tmem_empty[a], T2_EPI_WARPS * T4_EPI_GROUPS * (PAIR ? 2 : 1));
@@ -454,8 +472,8 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
           // the halves are walked in order: columns [0, W0) then [W0, BN); W0 is a multiple of 32 whenever W1 > 0
           const int slot = rit % T4_R_SLOTS;
           T2_WAIT(9, &bar->r_empty[slot], ((rit / T4_R_SLOTS) & 1) ^ 1);
-          ptx::mbar_arrive_expect_tx(&bar->r_full[slot], (uint32_t)T4_R_SLOT);
-          ptx::tma_load_2d(rring + slot * T4_R_SLOT, &p.mr, col0 + c0, row0, &bar->r_full[slot]);
+          ptx::mbar_arrive_expect_tx(&bar->r_full[t4_rfull(rit)], (uint32_t)T4_R_SLOT);
+          ptx::tma_load_2d(rring + slot * T4_R_SLOT, &p.mr, col0 + c0, row0, &bar->r_full[t4_rfull(rit)]);
         }
       }
     }
