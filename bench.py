@@ -424,7 +424,7 @@ def run_train_step(a, mpn, params, store, rng, batch, dev, world, copy_stream, s
         opt.step()
         return loss
 
-    for _ in range(5):
+    for _ in range(10):
         one()
     sync_all()
     k = max(3, min(a.steps, 20))
@@ -602,7 +602,9 @@ def main():
                     torch.cuda.current_stream().synchronize()
                 d2h_stream.synchronize()                 # the step's result is on the host (what loss.item() waits for)
 
-            for _ in range(5):                       # allocator / pinned-buffer pools reach their steady state
+            # allocator / pinned-buffer pools reach their steady state: with 5 steps the first loop of a process still left
+            # 17-33 ms of one-off work to the final synchronisation (scripts/e2e_tail_probe.py), with 15 it is gone
+            for _ in range(15):
                 e2e_step()
             sync_all()
             k = max(3, min(a.steps, 20))

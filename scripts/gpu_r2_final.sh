@@ -21,6 +21,6 @@ for f in ("bench", "bench_b50", "bench_ref"):
     if d.get("small_batch"): print("    small_batch", {k: (round(v, 1) if isinstance(v, float) else v) for k, v in d["small_batch"].items() if not isinstance(v, dict)}, "e2e", d["small_batch"].get("e2e"))
     if d.get("kernels"): print("   ", " ".join(f"{k}={v['ms_per_launch']*1e3:.1f}x{v['launches_per_step']:.0f}" for k, v in d["kernels"].items()))
 PY
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-small-batch"
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-small-batch --no-single-pass"
 echo "== ncu launch list"; $CMD > gpurun_out/ncu_plain.log 2>&1 && \
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_c_ncu_launches.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "list rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_f_ncu_launches.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "list rc=$?"
