@@ -207,17 +207,18 @@ class DeviceGraphStore:
         dg.n_atoms, dg.n_bonds, dg.n_mols = n_atoms, n_bonds, G
         ld_a, ld_b = (self.atom_fdim + 3) // 4 * 4, (self.bond_fdim + 3) // 4 * 4
         f32, i32 = dict(device=dev, dtype=torch.float32), dict(device=dev, dtype=torch.int32)
-        dg.f_atoms = torch.empty((n_atoms, ld_a), **f32)
-        dg.f_bonds = torch.empty((n_bonds, ld_b), **f32)
-        dg.w_atoms, dg.w_bonds = torch.empty(n_atoms, **f32), torch.empty(n_bonds, **f32)
-        dg.in_ptr = torch.empty(n_atoms + 1, **i32)
-        dg.in_idx, dg.out_idx = torch.empty(max(n_bonds - 1, 1), **i32), torch.empty(max(n_bonds - 1, 1), **i32)
-        dg.src, dg.rev, dg.dst = (torch.empty(n_bonds, **i32) for _ in range(3))
-        dg.mol_of = torch.empty(n_atoms, **i32)
+        E = _capi.empty_roomy                   # bucketed capacities: randomly drawn batches differ slightly in size
+        dg.f_atoms = E((n_atoms, ld_a), torch.float32, dev)
+        dg.f_bonds = E((n_bonds, ld_b), torch.float32, dev)
+        dg.w_atoms, dg.w_bonds = E((n_atoms,), torch.float32, dev), E((n_bonds,), torch.float32, dev)
+        dg.in_ptr = E((n_atoms + 1,), torch.int32, dev)
+        dg.in_idx, dg.out_idx = E((max(n_bonds - 1, 1),), torch.int32, dev), E((max(n_bonds - 1, 1),), torch.int32, dev)
+        dg.src, dg.rev, dg.dst = (E((n_bonds,), torch.int32, dev) for _ in range(3))
+        dg.mol_of = E((n_atoms,), torch.int32, dev)
         dg.dop = torch.empty(G, **f32)
         dg.a_start, dg.a_size = scopes[0], scopes[1]
         dg.flags = torch.zeros(4, **i32)
-        bond_mol = torch.empty(n_bonds, **i32)
+        bond_mol = E((n_bonds,), torch.int32, dev)
         p = _capi.ptr
         dg.struct = _capi.WdGraph(n_atoms, n_bonds, G, p(dg.f_atoms), p(dg.f_bonds), p(dg.w_atoms), p(dg.w_bonds),
                                   p(dg.in_ptr), p(dg.in_idx), p(dg.out_idx), p(dg.src), p(dg.rev), p(dg.dst), p(dg.mol_of),
