@@ -1,7 +1,8 @@
 // Device rebuild of BatchMolGraph's padded a2b [N_a,K] int64 into int32 CSR / reverse-CSR
 // (chemprop/features/featurization.py:757-813 builds the padded form on the host; the
 // reference consumes it through index_select_ND, chemprop/nn_utils.py:50-67).
-// Pure integer work: coalesced row reads, a three-phase exclusive scan, no atomics on the
+// Pure integer work: one thread per a2b row (K int64 ids, lanes K * 8 bytes apart -- rows are short and the whole
+// matrix is read once, 6 MB at B=4096), a three-phase exclusive scan, no atomics on the
 // data path (atomics only for the violation counter / max-degree statistic).
 #include "common.cuh"
 

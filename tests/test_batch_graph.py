@@ -91,3 +91,18 @@ def test_pack_arena_keeps_values_dtypes_and_shapes():
     assert end <= b._arena.numel()
     assert [torch.equal(u, v) for u, v in zip(a.get_components()[:7], b.get_components()[:7])] == [True] * 7
     assert b.pack_arena(pin=False) is b and b.fresh_view()._arena is b._arena          # idempotent, shared by views
+
+
+def test_bucketed_capacities_round_up_on_a_coarse_grid_and_leave_small_sizes_alone():
+    """_capi.bucket / empty_roomy: what the workspace and the store-assembled batches are allocated with, so that batches
+    whose sizes differ by a fraction of a per cent reuse the same cached blocks."""
+    import torch
+    from polymer_chemprop_b200 import _capi
+    assert [_capi.bucket(n) for n in (0, 1, 4096, (1 << 20) - 1)] == [0, 1, 4096, (1 << 20) - 1]
+    for n in (1 << 20, (1 << 20) + 1, 3_778_720_256, 81_000_000, 81_300_000):
+        b = _capi.bucket(n)
+        assert n <= b <= n * 1.0626 and b % (1 << (n.bit_length() - 5)) == 0
+    assert _capi.bucket(81_000_000) == _capi.bucket(81_300_000)              # 0.4 % apart: one bucket
+    t = _capi.empty_roomy((300_000, 4), torch.float32, "cpu")
+    assert t.shape == (300_000, 4) and t.is_contiguous() and t.untyped_storage().nbytes() == 4 * _capi.bucket(1_200_000)
+    assert _capi.empty_roomy((7,), torch.int32, "cpu").untyped_storage().nbytes() == 28
