@@ -284,7 +284,7 @@ class _EncoderFunction(torch.autograd.Function):
             ws_bytes = _capi.lib().wd_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
             if ws_bytes == 0:
                 _capi.check(_capi.WD_ERR_INVALID_ARG)
-            ws = torch.empty(_capi.bucket(ws_bytes), dtype=torch.uint8, device=dev)     # roomy: see _capi.bucket
+            ws = _capi.empty_high_water("ws", (ws_bytes,), torch.uint8, dev)       # capacity: largest bucket so far (_capi)
             out = torch.empty((dg.n_mols, enc.hidden_size), dtype=torch.float32, device=dev)
             ws_c = [t.detach().contiguous() if t is not None else None for t in (W_i, b_i, W_h, b_h, W_o, b_o)]
             weights = _capi.WdWeights(*[_capi.ptr(t) for t in ws_c])
@@ -403,7 +403,7 @@ class MPNEncoder(nn.Module):
             ws_bytes = L.wd_infer_workspace_bytes(C.byref(cfg), dg.n_atoms, dg.n_bonds, dg.n_mols)
             if ws_bytes == 0:
                 _capi.check(_capi.WD_ERR_INVALID_ARG)
-            ws = torch.empty(_capi.bucket(ws_bytes), dtype=torch.uint8, device=dev)     # roomy: see _capi.bucket
+            ws = _capi.empty_high_water("ws_infer", (ws_bytes,), torch.uint8, dev)  # capacity: largest bucket so far (_capi)
             out = torch.empty((dg.n_mols, self.hidden_size), dtype=torch.float32, device=dev)
             ws_c = [t.detach().contiguous() if t is not None else None
                     for t in (self.W_i.weight, self.W_i.bias, self.W_h.weight, self.W_h.bias, self.W_o.weight, self.W_o.bias)]

@@ -207,18 +207,19 @@ class DeviceGraphStore:
         dg.n_atoms, dg.n_bonds, dg.n_mols = n_atoms, n_bonds, G
         ld_a, ld_b = (self.atom_fdim + 3) // 4 * 4, (self.bond_fdim + 3) // 4 * 4
         f32, i32 = dict(device=dev, dtype=torch.float32), dict(device=dev, dtype=torch.int32)
-        E = _capi.empty_roomy                   # bucketed capacities: randomly drawn batches differ slightly in size
-        dg.f_atoms = E((n_atoms, ld_a), torch.float32, dev)
-        dg.f_bonds = E((n_bonds, ld_b), torch.float32, dev)
-        dg.w_atoms, dg.w_bonds = E((n_atoms,), torch.float32, dev), E((n_bonds,), torch.float32, dev)
-        dg.in_ptr = E((n_atoms + 1,), torch.int32, dev)
-        dg.in_idx, dg.out_idx = E((max(n_bonds - 1, 1),), torch.int32, dev), E((max(n_bonds - 1, 1),), torch.int32, dev)
-        dg.src, dg.rev, dg.dst = (E((n_bonds,), torch.int32, dev) for _ in range(3))
-        dg.mol_of = E((n_atoms,), torch.int32, dev)
+        H, sid = _capi.empty_high_water, id(self)        # capacities: largest bucket seen so far (see _capi)
+        dg.f_atoms = H((sid, "fa"), (n_atoms, ld_a), torch.float32, dev)
+        dg.f_bonds = H((sid, "fb"), (n_bonds, ld_b), torch.float32, dev)
+        dg.w_atoms, dg.w_bonds = H((sid, "wa"), (n_atoms,), torch.float32, dev), H((sid, "wb"), (n_bonds,), torch.float32, dev)
+        dg.in_ptr = H((sid, "ip"), (n_atoms + 1,), torch.int32, dev)
+        dg.in_idx = H((sid, "ii"), (max(n_bonds - 1, 1),), torch.int32, dev)
+        dg.out_idx = H((sid, "oi"), (max(n_bonds - 1, 1),), torch.int32, dev)
+        dg.src, dg.rev, dg.dst = (H((sid, k), (n_bonds,), torch.int32, dev) for k in ("src", "rev", "dst"))
+        dg.mol_of = H((sid, "mo"), (n_atoms,), torch.int32, dev)
         dg.dop = torch.empty(G, **f32)
         dg.a_start, dg.a_size = scopes[0], scopes[1]
         dg.flags = torch.zeros(4, **i32)
-        bond_mol = E((n_bonds,), torch.int32, dev)
+        bond_mol = H((sid, "bm"), (n_bonds,), torch.int32, dev)
         p = _capi.ptr
         dg.struct = _capi.WdGraph(n_atoms, n_bonds, G, p(dg.f_atoms), p(dg.f_bonds), p(dg.w_atoms), p(dg.w_bonds),
                                   p(dg.in_ptr), p(dg.in_idx), p(dg.out_idx), p(dg.src), p(dg.rev), p(dg.dst), p(dg.mol_of),

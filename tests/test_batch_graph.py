@@ -106,3 +106,17 @@ def test_bucketed_capacities_round_up_on_a_coarse_grid_and_leave_small_sizes_alo
     t = _capi.empty_roomy((300_000, 4), torch.float32, "cpu")
     assert t.shape == (300_000, 4) and t.is_contiguous() and t.untyped_storage().nbytes() == 4 * _capi.bucket(1_200_000)
     assert _capi.empty_roomy((7,), torch.int32, "cpu").untyped_storage().nbytes() == 28
+
+
+def test_high_water_capacities_grow_monotonically_and_ignore_much_smaller_requests():
+    import torch
+    from polymer_chemprop_b200 import _capi
+    H, key = _capi.empty_high_water, ("test", 1)
+    nbytes = lambda t: t.untyped_storage().nbytes()
+    a = H(key, (81_000_000,), torch.uint8, "cpu")
+    b = H(key, (80_000_000,), torch.uint8, "cpu")          # smaller, same order of magnitude: the largest capacity so far
+    c = H(key, (90_000_000,), torch.uint8, "cpu")          # larger: the capacity grows
+    d = H(key, (81_000_000,), torch.uint8, "cpu")
+    e = H(key, (1_000,), torch.uint8, "cpu")               # another workload: exact
+    assert nbytes(a) == nbytes(b) == _capi.bucket(81_000_000) and nbytes(c) == nbytes(d) == _capi.bucket(90_000_000)
+    assert nbytes(e) == 1_000 and [t.numel() for t in (a, b, c, d, e)] == [81_000_000, 80_000_000, 90_000_000, 81_000_000, 1_000]
