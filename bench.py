@@ -9,6 +9,7 @@ flat gradient when N > 1).  Rank 0 prints ONE JSON line.  See DESIGN.md "Measure
 """
 import argparse
 import ctypes as C
+import gc
 import json
 import os
 import subprocess
@@ -427,8 +428,10 @@ def run_train_step(a, mpn, params, store, rng, batch, dev, world, copy_stream, s
     for _ in range(10):
         one()
     sync_all()
-    k = max(3, min(a.steps, 20))
+    k = max(3, min(a.steps, 20 if batch >= 1024 else 200))     # small batches: more steps, one host stall must not be the mean
     walls = []
+    gc.collect()
+    gc.disable()                                  # as timeit does: no collector pause inside the timed steps
     t0 = time.perf_counter()
     for _ in range(k):
         ts = time.perf_counter()
@@ -436,13 +439,14 @@ def run_train_step(a, mpn, params, store, rng, batch, dev, world, copy_stream, s
         walls.append(1e3 * (time.perf_counter() - ts))     # host time to ENQUEUE the step (nothing is waited for)
     float(loss.detach())                          # the step's loss reaches the host
     sync_all()
+    gc.enable()
     te = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     if reducer is not None:
         reducer.detach()
     return {"value": world * batch / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()), "steps": k,
-            "host_enqueue_ms_median": float(np.median(walls)), "host_enqueue_ms": [round(w, 3) for w in walls],
+            "host_enqueue_ms_median": float(np.median(walls)), "host_enqueue_ms": [round(w, 3) for w in walls[:40]],
             "what": "store batch -> MPN -> fused FFN(300, 1) + masked MSE (wd_head_*) -> backward -> all-reduce -> FlatAdam, "
                     "wall clock; the step's loss is read on the host at the end of the timed run"}
 
@@ -607,14 +611,17 @@ def main():
             for _ in range(15):
                 e2e_step()
             sync_all()
-            k = max(3, min(a.steps, 20))
+            k = max(3, min(a.steps, 20 if G >= 1024 else 200))     # small batches: more steps, one host stall must not be the mean
             walls = []
+            gc.collect()
+            gc.disable()                             # as timeit does: no collector pause inside the timed steps
             t0 = time.perf_counter()
             for _ in range(k):
                 ts = time.perf_counter()
                 e2e_step()
                 walls.append(1e3 * (time.perf_counter() - ts))
             sync_all()
+            gc.enable()
             te = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
             if world > 1:
                 dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -623,13 +630,13 @@ def main():
             if native == "store":
                 return {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
                         "h2d_bytes_per_step": int(24 * G), "d2h_bytes_per_step": int(d2h), "steps": k,
-                        "ms_per_step_median": float(np.median(walls)), "step_ms": [round(w, 3) for w in walls], "store_bytes": int(store.nbytes), "host_sync": sync,
+                        "ms_per_step_median": float(np.median(walls)), "step_ms": [round(w, 3) for w in walls[:40]], "store_bytes": int(store.nbytes), "host_sync": sync,
                         "api": "DeviceGraphStore.batch(shuffled indices, copy stream) || MPN.forward(batch) + backward + "
                                "out -> pinned host; the featurised dataset is resident in HBM (uploaded once, outside the "
                                "timed region), each step uploads only the selected indices and their offsets"}
             return {"value": world * G / float(te.item()), "unit": UNIT, "ms_per_step": 1e3 * float(te.item()),
                     "h2d_bytes_per_step": int(nbytes(up) + (0 if native else G * 12)), "d2h_bytes_per_step": int(d2h),
-                    "steps": k, "ms_per_step_median": float(np.median(walls)), "step_ms": [round(w, 3) for w in walls], "host_sync": sync,
+                    "steps": k, "ms_per_step_median": float(np.median(walls)), "step_ms": [round(w, 3) for w in walls[:40]], "host_sync": sync,
                     "api": "MPN.forward(batch) + backward + out -> pinned host || DeviceGraph.prefetch(next batch of "
                            "pinned CPU tensors, copy stream)",
                     "upload": ("f_atoms + bond-only tail of f_bonds (BatchMolGraph.f_bonds_tail) + weights + indices; "
