@@ -59,6 +59,13 @@ constexpr int T4_XR = 4 * T4_XFORM_WARPS, T4_XJ = TC_BM / T4_XR;   // transform:
 #ifndef WD_T4_EPI_GROUPS
 #define WD_T4_EPI_GROUPS 2
 #endif
+#ifndef WD_T4_MERGE
+#define WD_T4_MERGE 1          // 1: one bulk copy per packed image (the rows of both accumulator halves are contiguous) instead of
+                               // one per half.  Same bytes, half the copy operations: depth-step contraction 309 -> 288 us, step
+                               // 2.87 -> 2.80 ms (profiles/r2_fwd_abl.log section J) -- the per-operation cost of the copy engine,
+                               // not the bandwidth, is what the "no weight copies" ablation had measured
+#endif
+constexpr bool T4_MERGE = WD_T4_MERGE != 0;
 constexpr int T4_EPI_GROUPS = WD_T4_EPI_GROUPS, T4_EPI2_W0 = T4_XFORM_W0 + T4_XFORM_WARPS;
 constexpr int T4_THREADS = 32 * (T4_EPI2_W0 + (T4_EPI_GROUPS - 1) * 4);
 constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_R_SLOTS = 3;
@@ -486,6 +493,14 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
         for (int kc = 0; kc < p.KC; ++kc) {
           for (int part = 0; part < parts; ++part) {
             const float* img = p.Bp + (((int64_t)nt * p.KC + kc) * parts + part) * p.BN * 32;
+            if (T4_MERGE && !PAIR) {          // one copy per image: both accumulator halves' rows are contiguous
+              const int slot = u % B_STAGES;
+              T2_WAIT(3, &bar->b_empty[slot], ((u / B_STAGES) & 1) ^ 1);
+              ptx::mbar_arrive_expect_tx(&bar->b_full[slot], (uint32_t)(p.BN * 128));
+              ptx::bulk_g2s(ringB + slot * b_stage, img, (uint32_t)(p.BN * 128), &bar->b_full[slot]);
+              ++u;
+              continue;
+            }
             for (int hb = 0; hb < nh; ++hb, ++u) {
               const int slot = u % nslots;
               T2_WAIT(3, &bar->b_empty[slot], ((u / nslots) & 1) ^ 1);
@@ -529,6 +544,18 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
         for (int part = 0; part < parts; ++part) {
           uint32_t b_addr[2] = {0u, 0u}, d[2] = {0u, 0u};
           int slots[2] = {0, 0};
+          if (T4_MERGE && !PAIR) {
+            const int slot = u % B_STAGES;
+            T2_WAIT(6, &bar->b_full[slot], (u / B_STAGES) & 1);
+            ++u;
+            for (int hb = 0; hb < nh; ++hb) {
+              slots[hb] = slot;
+              const uint32_t gb = g0 + hb;
+              if (kc == 0 && part == 0) T2_WAIT(4, &bar->tmem_empty[gb % 3], ((gb / 3) & 1) ^ 1);
+              b_addr[hb] = ptx::desc_lo_sw128(ringB_u + slot * b_stage + (hb ? h1_off : 0));
+              d[hb] = tmem_u + (gb % 3) * T4_HALF;
+            }
+          } else
           for (int hb = 0; hb < nh; ++hb, ++u) {
             const int slot = u % nslots;
             slots[hb] = slot;
@@ -564,6 +591,8 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
                 }
           }
           // (PAIR: every completion below is committed to the barrier at the same offset in BOTH CTAs)
+          if (T4_MERGE && !PAIR) ptx::tc_commit_elect(&bar->b_empty[slots[0]]);
+          else
           for (int hb = 0; hb < nh; ++hb) { if (PAIR) ptx::tc_commit_elect_pair(&bar->b_empty[slots[hb]]); else ptx::tc_commit_elect(&bar->b_empty[slots[hb]]); }
           __syncwarp();
         }
