@@ -229,19 +229,26 @@ int bind_packed(const WdConfig& c, Layout& L, void* ws) {
 // until then.  The order of the additions inside a job is fixed, so the result does not depend on the batching.
 struct Reducer {
   ReduceJobs jobs{};
-  unsigned blocks = 0;
+  bool vec = true;        // every job so far has n % 4 == 0 and 16-byte aligned partials: four outputs per thread
   int add(const float* P, float* out, int64_t n, int Z) {
     if (jobs.count >= RP_MAX_JOBS) return fail(WD_ERR_UNSUPPORTED, "too many reductions in one pass");
-    jobs.j[jobs.count++] = ReduceJob{P, out, n, Z, blocks};
-    blocks += (unsigned)ceil_div(n, RP_COLS);
+    jobs.j[jobs.count++] = ReduceJob{P, out, n, Z, 0u};
+    vec = vec && n % 4 == 0 && (reinterpret_cast<uintptr_t>(P) & 15) == 0;
     return WD_OK;
   }
   int run(cudaStream_t s) {
     if (jobs.count == 0) return WD_OK;
     ProfScope ps(WD_PROF_REDUCE);
-    WD_LAUNCH(k_reduce_partials, blocks, RP_COLS * RP_GROUPS, 0, s, jobs);
+    const int per_block = RP_COLS * (vec ? 4 : 1);
+    unsigned blocks = 0;
+    for (int k = 0; k < jobs.count; ++k) {
+      jobs.j[k].block0 = blocks;
+      blocks += (unsigned)ceil_div(jobs.j[k].n, per_block);
+    }
+    if (vec) WD_LAUNCH(k_reduce_partials<4>, blocks, RP_COLS * RP_GROUPS, 0, s, jobs);
+    else     WD_LAUNCH(k_reduce_partials<1>, blocks, RP_COLS * RP_GROUPS, 0, s, jobs);
     jobs.count = 0;
-    blocks = 0;
+    vec = true;
     return WD_OK;
   }
 };
@@ -259,7 +266,10 @@ int colsum(cudaStream_t s, const float* X, int ldx, float* P, float* out, int64_
   const int Z = colsum_chunks(R);
   int64_t rpc = ceil_div(R, Z);
   { ProfScope ps(WD_PROF_REDUCE);
-  WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc); }
+  if (N % 4 == 0 && ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0)
+    WD_LAUNCH(k_colsum_partial4, dim3((unsigned)ceil_div(N, 4 * 96), (unsigned)Z), 96, 0, s, X, ldx, P, R, N, rpc);
+  else
+    WD_LAUNCH(k_colsum_partial, dim3((unsigned)ceil_div(N, 128), (unsigned)Z), 128, 0, s, X, ldx, P, R, N, rpc); }
   return red.add(P, out, N, Z);
 }
 

@@ -161,7 +161,7 @@ int head_backward_impl(const WdHead& h, const HeadLayout& L, const float* X, int
   unsigned blocks = 0;
   auto flush = [&]() -> int {
     if (jobs.count == 0) return WD_OK;
-    WD_LAUNCH(k_reduce_partials, blocks, RP_COLS * RP_GROUPS, 0, s, jobs);
+    WD_LAUNCH(k_reduce_partials<1>, blocks, RP_COLS * RP_GROUPS, 0, s, jobs);
     jobs.count = 0;
     blocks = 0;
     return WD_OK;

@@ -191,6 +191,43 @@ static __global__ void k_colsum_partial(const float* __restrict__ X, int ldx, fl
   for (; r < r_end; ++r) s0 += __ldg(X + r * ldx + n);
   P[(int64_t)blockIdx.y * N + n] = (s0 + s1) + (s2 + s3);
 }
+// the same sums with four columns per thread (16-byte loads, eight rows in flight); needs N % 4 == 0 and 16-byte aligned
+// rows.  Per column the additions happen in the same order as above (rows r, r + 4, ... into accumulator r % 4), so
+// the bits are the same.
+static __global__ void k_colsum_partial4(const float* __restrict__ X, int ldx, float* __restrict__ P,
+                                  int64_t R, int N, int64_t rows_per_chunk) {
+  pdl_prologue();   // programmatic dependent launch: see common.cuh
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (n >= N) return;
+  const int64_t r_begin = (int64_t)blockIdx.y * rows_per_chunk, r_end = min(R, r_begin + rows_per_chunk);
+  float4 s[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) s[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  int64_t r = r_begin;
+  for (; r + 8 <= r_end; r += 8) {
+    float4 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = ldg4(X + (r + k) * ldx + n);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k & 3] = make_float4(s[k & 3].x + v[k].x, s[k & 3].y + v[k].y, s[k & 3].z + v[k].z, s[k & 3].w + v[k].w);
+  }
+  for (; r + 4 <= r_end; r += 4) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 v = ldg4(X + (r + k) * ldx + n);
+      s[k] = make_float4(s[k].x + v.x, s[k].y + v.y, s[k].z + v.z, s[k].w + v.w);
+    }
+  }
+  for (; r < r_end; ++r) {
+    const float4 v = ldg4(X + r * ldx + n);
+    s[0] = make_float4(s[0].x + v.x, s[0].y + v.y, s[0].z + v.z, s[0].w + v.w);
+  }
+  float* o = P + (int64_t)blockIdx.y * N + n;
+  o[0] = (s[0].x + s[1].x) + (s[2].x + s[3].x);
+  o[1] = (s[0].y + s[1].y) + (s[2].y + s[3].y);
+  o[2] = (s[0].z + s[1].z) + (s[2].z + s[3].z);
+  o[3] = (s[0].w + s[1].w) + (s[2].w + s[3].w);
+}
 
 // out[i] = sum_z P[z][i].  The Z partials are split into RP_GROUPS contiguous ranges summed concurrently
 // (ascending z inside a range, four independent accumulators), then the range sums are added in ascending order:
@@ -211,9 +248,12 @@ struct ReduceJobs {
   ReduceJob j[RP_MAX_JOBS];
   int count;
 };
+// V = 4: every thread owns four consecutive outputs and reads the partials as 16-byte words (all jobs need n % 4 == 0
+// and 16-byte aligned partials); the order of additions per output is the same as for V = 1, hence the same bits.
+template <int V>
 static __global__ void __launch_bounds__(RP_COLS * RP_GROUPS) k_reduce_partials(const ReduceJobs jobs) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
-  __shared__ float part[RP_GROUPS][RP_COLS];
+  __shared__ float part[RP_GROUPS][RP_COLS * V];
   int ji = 0;
 #pragma unroll
   for (int k = 1; k < RP_MAX_JOBS; ++k)
@@ -223,24 +263,35 @@ static __global__ void __launch_bounds__(RP_COLS * RP_GROUPS) k_reduce_partials(
   const int64_t n = jobs.j[ji].n;
   const int Z = jobs.j[ji].Z;
   const int tx = threadIdx.x & (RP_COLS - 1), ty = threadIdx.x / RP_COLS;
-  const int64_t i = (int64_t)(blockIdx.x - jobs.j[ji].block0) * RP_COLS + tx;
+  const int64_t i = ((int64_t)(blockIdx.x - jobs.j[ji].block0) * RP_COLS + tx) * V;
   const int z0 = (int)((int64_t)Z * ty / RP_GROUPS), z1 = (int)((int64_t)Z * (ty + 1) / RP_GROUPS);
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  float s0[V], s1[V], s2[V], s3[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) s0[v] = s1[v] = s2[v] = s3[v] = 0.f;
+  auto add = [&](float (&acc)[V], int z) {
+    if (V == 4) {
+      const float4 x = *reinterpret_cast<const float4*>(P + (int64_t)z * n + i);
+      acc[0] += x.x; acc[1 % V] += x.y; acc[2 % V] += x.z; acc[3 % V] += x.w;
+    } else {
+      acc[0] += P[(int64_t)z * n + i];
+    }
+  };
   if (i < n) {
     int z = z0;
-    for (; z + 4 <= z1; z += 4) {
-      s0 += P[(int64_t)(z + 0) * n + i]; s1 += P[(int64_t)(z + 1) * n + i];
-      s2 += P[(int64_t)(z + 2) * n + i]; s3 += P[(int64_t)(z + 3) * n + i];
-    }
-    for (; z < z1; ++z) s0 += P[(int64_t)z * n + i];
+    for (; z + 4 <= z1; z += 4) { add(s0, z); add(s1, z + 1); add(s2, z + 2); add(s3, z + 3); }
+    for (; z < z1; ++z) add(s0, z);
   }
-  part[ty][tx] = (s0 + s1) + (s2 + s3);
+#pragma unroll
+  for (int v = 0; v < V; ++v) part[ty][tx * V + v] = (s0[v] + s1[v]) + (s2[v] + s3[v]);
   __syncthreads();
   if (ty == 0 && i < n) {
-    float s = part[0][tx];
 #pragma unroll
-    for (int g = 1; g < RP_GROUPS; ++g) s += part[g][tx];
-    out[i] = s;
+    for (int v = 0; v < V; ++v) {
+      float t = part[0][tx * V + v];
+#pragma unroll
+      for (int g = 1; g < RP_GROUPS; ++g) t += part[g][tx * V + v];
+      out[i + v] = t;
+    }
   }
 }
 
