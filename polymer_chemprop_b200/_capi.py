@@ -208,8 +208,8 @@ def empty_high_water(key, shape, dtype, device):
     cap, want = _HIGH_WATER.get(k, 0), bucket(n)
     if want < cap // 2:          # a much smaller batch than the largest so far (another workload): no padding up to it
         cap = want
-    else:
-        cap = max(cap, want)
+    elif n > cap:                # a new maximum: grow with 3 % headroom, so that the next slightly larger batch still fits
+        cap = bucket(n + n // 32) if n >= (1 << 20) else want
         _HIGH_WATER[k] = cap
     t = torch.empty(cap, dtype=dtype, device=device)
     return (t if cap == n else t[:n]).view(shape)

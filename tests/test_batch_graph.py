@@ -113,10 +113,14 @@ def test_high_water_capacities_grow_monotonically_and_ignore_much_smaller_reques
     from polymer_chemprop_b200 import _capi
     H, key = _capi.empty_high_water, ("test", 1)
     nbytes = lambda t: t.untyped_storage().nbytes()
-    a = H(key, (81_000_000,), torch.uint8, "cpu")
-    b = H(key, (80_000_000,), torch.uint8, "cpu")          # smaller, same order of magnitude: the largest capacity so far
-    c = H(key, (90_000_000,), torch.uint8, "cpu")          # larger: the capacity grows
-    d = H(key, (81_000_000,), torch.uint8, "cpu")
-    e = H(key, (1_000,), torch.uint8, "cpu")               # another workload: exact
-    assert nbytes(a) == nbytes(b) == _capi.bucket(81_000_000) and nbytes(c) == nbytes(d) == _capi.bucket(90_000_000)
-    assert nbytes(e) == 1_000 and [t.numel() for t in (a, b, c, d, e)] == [81_000_000, 80_000_000, 90_000_000, 81_000_000, 1_000]
+    a = H(key, (81_000_000,), torch.uint8, "cpu")          # first request: its bucket with 3 % headroom
+    b = H(key, (80_000_000,), torch.uint8, "cpu")          # smaller, same order of magnitude: the capacity so far
+    c = H(key, (82_000_000,), torch.uint8, "cpu")          # 1.2 % larger: still inside the headroom
+    d = H(key, (90_000_000,), torch.uint8, "cpu")          # a new maximum beyond it: the capacity grows
+    e = H(key, (81_000_000,), torch.uint8, "cpu")
+    f = H(key, (1_000,), torch.uint8, "cpu")               # another workload: exact
+    cap0 = _capi.bucket(81_000_000 + 81_000_000 // 32)
+    assert nbytes(a) == nbytes(b) == nbytes(c) == cap0 and 82_000_000 <= cap0 <= 81_000_000 * 1.1
+    assert nbytes(d) == nbytes(e) == _capi.bucket(90_000_000 + 90_000_000 // 32) > cap0
+    assert nbytes(f) == 1_000
+    assert [t.numel() for t in (a, b, c, d, e, f)] == [81_000_000, 80_000_000, 82_000_000, 90_000_000, 81_000_000, 1_000]
