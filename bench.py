@@ -258,7 +258,9 @@ def algorithmic_bytes(Na, Nb, G, h, Fa, Fb, d, sign_bits=False):
     A = B if sign_bits else P                    # what the message gradient reads for act'
     steps = max(d - 1, 1)
     depth_total = ((3 * P + Q + B) + (d - 2) * (4 * P + Q + B)) if d > 1 else 0.0    # t=1 reads I once; every step writes S_t
-    if d > 1:
+    if d == 3:     # bench.py's models have no W_h bias: the middle step leaves the running sum to the last one (encoder.cu: defer_sum)
+        msg_total = (P + A + Q) + (2 * P + A + Q) + (4 * P + A + Q)
+    elif d > 1:
         msg_total = (P + A + Q) + (d - 2) * (4 * P + A + Q) + (3 * P + A + Q)     # first / middle / last step
     else:
         msg_total = P + A + Q

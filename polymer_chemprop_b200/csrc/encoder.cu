@@ -365,7 +365,7 @@ int forward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void* 
 template <int ACT, bool PREACT, bool HAS_DS, bool WRITE_DZ, bool WRITE_DI>
 int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const float* dA, const float* dS,
                  const float* Y, int ld, float* dZ, const float* dI_in, float* dI, const Dropout& drop,
-                 const SignBits& sb) {
+                 const SignBits& sb, const float* dI_in2 = nullptr) {
   const int nc4 = ld / 4;
   const int64_t Nb = g.n_bonds;
   ProfScope ps(WD_PROF_MSG_GRAD);
@@ -374,18 +374,18 @@ int message_grad(const WdConfig& c, cudaStream_t s, const WdGraph& g, const floa
   if (kRelu && sb.p != nullptr) {
     if (c.undirected && HAS_DS)
       WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, kRelu>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
-                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb, rpb);
+                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI_in2, dI, Nb, nc4, drop, sb, rpb);
     else
       WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, kRelu>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
-                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, sb, rpb);
+                ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI_in2, dI, Nb, nc4, drop, sb, rpb);
     return WD_OK;
   }
   if (c.undirected && HAS_DS)
     WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, true, WRITE_DZ, WRITE_DI, false>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
-              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{}, rpb);
+              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI_in2, dI, Nb, nc4, drop, SignBits{}, rpb);
   else
     WD_LAUNCH((k_message_grad<ACT, PREACT, HAS_DS, false, WRITE_DZ, WRITE_DI, false>), (unsigned)ceil_div(Nb, rpb), 256, 0, s, dA, dS, Y,
-              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI, Nb, nc4, drop, SignBits{}, rpb);
+              ld, g.w_bonds, g.dst, g.rev, dZ, dI_in, dI_in2, dI, Nb, nc4, drop, SignBits{}, rpb);
   return WD_OK;
 }
 
@@ -480,6 +480,11 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   // `sum` points at sum_{t' >= t} dZ_t': the first step's dZ itself (no separate dI write), dI afterwards
   float* dZbuf[2] = {L.p(ws, L.dZ), L.p(ws, L.dZ2)};
   const float* sum = nullptr;
+  // depth 3 without a W_h bias: both dZ_2 and dZ_1 are still in their buffers when the last step runs, so the running
+  // sum dI = dZ_2 + dZ_1 is not materialised by the middle step (one read and one write of [N_b, h] less per pass);
+  // the last step forms (dZ_2 + dZ_1) + dZ_0 itself -- the same association, hence the same bits
+  const bool defer_sum = d == 3 && !(c.bias && gr.db_h);
+  const float* sum2 = nullptr;
   for (int t = d - 1; t >= 1; --t) {
     float* dZ = dZbuf[(d - 1 - t) & 1];
     const float* M_t = L.p(ws, L.M) + (int64_t)(t - 1) * L.szB;
@@ -490,6 +495,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     const SignBits sg = sign_bits(L, ws, Nb, t, L.pWh);
     if (d - 1 - t >= 2) WD_TRY(sd.join());   // this step overwrites the dZ buffer the weight gradient of two steps ago reads
     if (t == d - 1) { WD_TRY((message_grad<ACT, false, false, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI, make_dropout(c, t), sg))); sum = dZ; }
+    else if (defer_sum) { WD_TRY((message_grad<ACT, false, true, true, false>(c, s, g, dA, dS, M_t, ld, dZ, nullptr, dI, make_dropout(c, t), sg))); sum2 = dZ; }
     else            { WD_TRY((message_grad<ACT, false, true, true, true>(c, s, g, dA, dS, M_t, ld, dZ, sum, dI, make_dropout(c, t), sg))); sum = dI; }
     // dW_h += dZ_t^T S_t, S_t = A_t[b2a] - U_{t-1}[b2revb]: recomputed by the gather (FP32 path) or read back (TF32 path)
     const float* u = M_prev;
@@ -523,7 +529,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
     { ProfScope ps(WD_PROF_DW);
     WD_TRY(red.add(Ph, gr.dW_h, (int64_t)h * h, (d - 1) * Zh));
     if (c.bias && gr.db_h) WD_TRY(colsum(s, sum, ld, Pcol + pcol, gr.db_h, Nb, h, red)); }  // sum == sum_{t>=1} dZ_t here
-    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI, Dropout{}, sign_bits(L, ws, Nb, 0, L.pWi))));
+    WD_TRY((message_grad<ACT, true, true, false, true>(c, s, g, dA, dS, I, ld, nullptr, sum, dI, Dropout{}, sign_bits(L, ws, Nb, 0, L.pWi), sum2)));
   } else {
     WD_CUDA_OK(cudaMemsetAsync(gr.dW_h, 0, sizeof(float) * h * h, s));
     if (c.bias && gr.db_h) WD_CUDA_OK(cudaMemsetAsync(gr.db_h, 0, sizeof(float) * h, s));

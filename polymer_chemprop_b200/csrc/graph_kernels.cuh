@@ -66,7 +66,8 @@ __global__ void k_symmetrize(const float* __restrict__ X, int ld, const int32_t*
 //   g(b)  = w_b * dA[dst b] - dS[rev b]              (dS absent for the last step: HAS_DS = false)
 //   UNDIRECTED && HAS_DS:  g(b) = (g(b) + g(rev b)) / 2
 //   dZ[b] = g(b) * act'(Y[b])   with Y = M_t (PREACT: Y = act(I))
-//   dI[b] = (dI_in ? dI_in[b] : 0) + dZ[b]     (WRITE_DI; dI_in may alias dI or be the previous step's dZ)
+//   dI[b] = (dI_in ? dI_in[b] (+ dI_in2[b]) : 0) + dZ[b]     (WRITE_DI; dI_in may alias dI or be an earlier step's dZ;
+//                                                            dI_in2: a second earlier dZ, see backward_impl)
 // WRITE_DZ = false for the last step (nothing reads dZ_0), WRITE_DI = false for the first one (dI == dZ then).
 constexpr int MG_ROWS = 64;   // most rows per block of k_message_grad (fewer when the batch is small: see message_grad())
 
@@ -76,7 +77,7 @@ template <int ACT, bool PREACT, bool HAS_DS, bool UNDIRECTED, bool WRITE_DZ, boo
 __global__ void k_message_grad(const float* __restrict__ dA, const float* __restrict__ dS,
                                const float* __restrict__ Y, int ld, const float* __restrict__ w,
                                const int32_t* __restrict__ dst, const int32_t* __restrict__ rev,
-                               float* __restrict__ dZ, const float* dI_in, float* dI, int64_t n_rows, int nc4,
+                               float* __restrict__ dZ, const float* dI_in, const float* dI_in2, float* dI, int64_t n_rows, int nc4,
                                Dropout drop, SignBits sb, int rows_per_block) {
   pdl_prologue();   // programmatic dependent launch: see common.cuh
   // A block walks rows_per_block (<= MG_ROWS) consecutive rows as one flat run of (row, column quad) elements, 256 at a time: adjacent
@@ -123,7 +124,11 @@ __global__ void k_message_grad(const float* __restrict__ dA, const float* __rest
   if (WRITE_DZ) st4(dZ + b * ld + c, dz);
   if (WRITE_DI) {
     if (dI_in != nullptr) {
-      const float4 di = *reinterpret_cast<const float4*>(dI_in + b * ld + c);
+      float4 di = *reinterpret_cast<const float4*>(dI_in + b * ld + c);
+      if (dI_in2 != nullptr) {                 // (dZ_a + dZ_b) first: the same association as the running sum it replaces
+        const float4 d2 = *reinterpret_cast<const float4*>(dI_in2 + b * ld + c);
+        di = make_float4(di.x + d2.x, di.y + d2.y, di.z + d2.z, di.w + d2.w);
+      }
       dz = make_float4(di.x + dz.x, di.y + dz.y, di.z + dz.z, di.w + dz.w);
     }
     st4(dI + b * ld + c, dz);
