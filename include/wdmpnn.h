@@ -49,6 +49,8 @@ enum { WD_MATH_FP32 = 0, WD_MATH_TF32 = 1, WD_MATH_TF32X3 = 2 };
 #define WD_FLAG_NO_GRAPH 2u     /* never replay the call's launches through a CUDA graph (see wd_encoder_forward)     */
 #define WD_FLAG_NO_SIDE_BRANCH 4u /* captured backward pass: keep the weight-gradient kernels in the main chain instead */
                                 /* of on a parallel branch of the graph (A/B and test switch; results are identical)  */
+#define WD_FLAG_NO_DEFER_SUM 8u /* backward, depth 3 without a W_h bias: materialise the running sum dI in the middle step */
+                                /* as every other configuration does (A/B and test switch; results are identical)     */
 
 /* Encoder configuration == the TrainArgs fields MPNEncoder.__init__ reads (mpn.py:24-35). */
 typedef struct WdConfig {

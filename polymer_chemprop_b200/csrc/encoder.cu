@@ -483,7 +483,7 @@ int backward_impl(const WdGraph& g, const WdWeights& w, const WdConfig& c, void*
   // depth 3 without a W_h bias: both dZ_2 and dZ_1 are still in their buffers when the last step runs, so the running
   // sum dI = dZ_2 + dZ_1 is not materialised by the middle step (one read and one write of [N_b, h] less per pass);
   // the last step forms (dZ_2 + dZ_1) + dZ_0 itself -- the same association, hence the same bits
-  const bool defer_sum = d == 3 && !(c.bias && gr.db_h);
+  const bool defer_sum = d == 3 && !(c.bias && gr.db_h) && !(c.flags & WD_FLAG_NO_DEFER_SUM);
   const float* sum2 = nullptr;
   for (int t = d - 1; t >= 1; --t) {
     float* dZ = dZbuf[(d - 1 - t) & 1];

@@ -390,6 +390,8 @@ class MPNEncoder(nn.Module):
             flags |= _capi.FLAG_NO_GRAPH
         if os.environ.get("WD_SIDE_BRANCH", "1") == "0":
             flags |= _capi.FLAG_NO_SIDE_BRANCH
+        if os.environ.get("WD_DEFER_SUM", "1") == "0":
+            flags |= _capi.FLAG_NO_DEFER_SUM
         return _capi.WdConfig(self.hidden_size, dg.atom_fdim, dg.bond_fdim, self.depth,
                               _capi.ACTIVATIONS[self.activation], _capi.AGGREGATIONS[self.aggregation],
                               int(bool(self.undirected)), int(bool(self.bias)),

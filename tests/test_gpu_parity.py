@@ -331,3 +331,23 @@ def test_small_batches_run_as_one_cuda_graph_per_pass_with_the_same_bits(mode, d
             assert torch.equal(o1, o0)
             for k in gr1:
                 assert torch.equal(gr1[k], gr0[k]), (other, k)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
+def test_deferred_gradient_sum_gives_the_same_bits_as_the_running_sum(mode, monkeypatch):
+    """Depth 3 without a W_h bias: the middle message-gradient step leaves dI = dZ_2 + dZ_1 to the last step, which forms
+    (dZ_2 + dZ_1) + dZ_0 from the two dZ buffers (csrc/encoder.cu: defer_sum) -- the same association as the running
+    sum, so every gradient agrees bit for bit with WD_DEFER_SUM=0 (WdConfig.flags & WD_FLAG_NO_DEFER_SUM)."""
+    bmg = BatchMolGraph(synth.make_graphs("copolymer", 200, 91, random_edge_weights=True) + [synth.empty_graph()])
+    torch.manual_seed(6)
+    model = MPN(_util.make_args(hidden_size=300, depth=3, wd_math_mode=mode), atom_fdim=bmg.atom_fdim,
+                bond_fdim=bmg.bond_fdim).to(DEV)
+    d_out = torch.randn(len(bmg.a_scope), 300, generator=torch.Generator().manual_seed(7))
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("WD_DEFER_SUM", flag)
+        res[flag] = _util.run_fwd_bwd(model, bmg, d_out)
+        assert bool(model.encoder[0].last_config.flags & _capi.FLAG_NO_DEFER_SUM) == (flag == "0")
+    assert torch.equal(res["1"][0], res["0"][0])
+    for k in res["1"][1]:
+        assert torch.equal(res["1"][1][k], res["0"][1][k]), k
