@@ -558,6 +558,16 @@ def main():
 
     # ---- end to end: pinned host tensors -> H2D -> feature expansion + CSR build -> fwd+bwd -> D2H of the output
     e2e, e2e_full, e2e_store, e2e_step_sync = None, None, None, None
+    # the look-ahead loop keeps two steps' workspaces alive at once (the previous step's output is still on its way to
+    # the host when the next forward pass allocates): a configuration whose training workspace is over ~45 % of the
+    # device memory (configs[3]: 92 GB at h=2400, d=6, B=8192) has no such loop on one GPU -- say so instead of failing
+    e2e_skipped = None
+    if not a.no_e2e:
+        ws_train = int(lib.wd_workspace_bytes(C.byref(model.encoder[0].last_config), Na, Nb, G))
+        if 2.2 * ws_train > torch.cuda.get_device_properties(dev).total_memory:
+            a.no_e2e = True
+            e2e_skipped = (f"training workspace {ws_train / 2**30:.1f} GiB: two steps in flight do not fit this GPU; "
+                           "device-resident figures only")
     if not a.no_e2e:
         comps = bmg.get_components()
         pinned = tuple(x.pin_memory() for x in comps[:7]) + tuple(comps[7:])
@@ -809,7 +819,8 @@ def main():
                 "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[a.math],
                 "data": "synthetic",
                 "config": base_config(a, world, G, Na, Nb),
-                "options": {"math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0", "sign_bits": sign_bits},
+                "options": {"math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0", "sign_bits": sign_bits,
+                            "e2e_skipped": e2e_skipped},
                 "edge_msgs_per_s": world * (Nb - 1) * max(a.depth - 1, 0) / (ms_step * 1e-3),
                 "roofline": roof, "kernels": kernels,
                 "step_hbm": {"alg_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,

@@ -68,13 +68,19 @@ constexpr int T4_XR = 4 * T4_XFORM_WARPS, T4_XJ = TC_BM / T4_XR;   // transform:
 constexpr bool T4_MERGE = WD_T4_MERGE != 0;
 constexpr int T4_EPI_GROUPS = WD_T4_EPI_GROUPS, T4_EPI2_W0 = T4_XFORM_W0 + T4_XFORM_WARPS;
 constexpr int T4_THREADS = 32 * (T4_EPI2_W0 + (T4_EPI_GROUPS - 1) * 4);
-constexpr int T4_A_STAGES = 3, T4_B_STAGES = 2, T4_R_SLOTS = 3;
+#ifndef WD_T4_A_STAGES
+#define WD_T4_A_STAGES 3
+#endif
+#ifndef WD_T4_MAX_BN
+#define WD_T4_MAX_BN 304
+#endif
+constexpr int T4_A_STAGES = WD_T4_A_STAGES, T4_B_STAGES = 2, T4_R_SLOTS = 3;
 constexpr int T4_B_SLOTS = 4 * T4_B_STAGES;      // weight-ring units: 2 per stage; a CTA pair keeps half of each unit, so twice as many fit
 constexpr int T4_X1_ROWS = 132, T4_X1_LEAD = 2;   // TMA box of the subtrahend rows: [row0 - 2, row0 + 130)
 constexpr int T4_X1_STAGE = 17 * 1024;            // >= T4_X1_ROWS * 128 bytes, keeps the stages 1024-byte aligned
 constexpr int T4_A_STAGE = TC_A_STAGE + T4_X1_STAGE;   // minuend rows / a_hi (128 x 128 bytes) + subtrahend rows / a_lo
 constexpr int T4_R_SLOT = TC_BM * 128;            // residual / staging slot: 128 rows x 32 floats, swizzled
-constexpr int T4_HALF = 160, T4_MAX_BN = 304;     // accumulator half / widest column tile
+constexpr int T4_HALF = 160, T4_MAX_BN = WD_T4_MAX_BN;     // accumulator half / widest column tile
 static_assert(T4_LOAD_WARPS * 32 == TC_BM && (T4_XFORM_WARPS == 4 || T4_XFORM_WARPS == 8), "8 threads per row");
 
 struct T4Barriers {
@@ -398,7 +404,9 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
           const int rem = (p.K - k) * 4;
           const uint32_t valid = rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u);
           const uint32_t d0 = ring_u32 + s * T4_A_STAGE + po;
-          if (p.x1_tma) {                           // subtrahend rows: one TMA box; minuend rows: gathered cp.async
+          if (WD_ABL & 32) {                        // timing ablation: no operand copies
+            if (p.x1_tma && t == 0) ptx::mbar_arrive(&bar->raw_full[s]);
+          } else if (p.x1_tma) {                    // subtrahend rows: one TMA box; minuend rows: gathered cp.async
             if (t == 0) {
               ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)(T4_X1_ROWS * 128));
               ptx::tma_load_2d(ringA + s * T4_A_STAGE + TC_A_STAGE, &p.mx1, kc * TC_BK, (int)row0 - T4_X1_LEAD,
@@ -496,6 +504,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
             if (T4_MERGE && !PAIR) {          // one copy per image: both accumulator halves' rows are contiguous
               const int slot = u % B_STAGES;
               T2_WAIT(3, &bar->b_empty[slot], ((u / B_STAGES) & 1) ^ 1);
+              if (WD_ABL & 4096) { ptx::mbar_arrive(&bar->b_full[slot]); ++u; continue; }     // timing ablation: no weight copies
               ptx::mbar_arrive_expect_tx(&bar->b_full[slot], (uint32_t)(p.BN * 128));
               ptx::bulk_g2s(ringB + slot * b_stage, img, (uint32_t)(p.BN * 128), &bar->b_full[slot]);
               ++u;

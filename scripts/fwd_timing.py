@@ -45,8 +45,8 @@ def gemm(M, N, K, lda, epi, mode):
     report(f"plain GEMM M={M} N={N} K={K} epi={epi} mode={mode}: {e0.elapsed_time(e1) * 1e3:.0f} us incl. pack")
 
 
-def depth_step(mode, batch=4096):
-    a = types.SimpleNamespace(hidden=300, depth=3, math=mode)
+def depth_step(mode, batch=4096, hidden=300, depth=3):
+    a = types.SimpleNamespace(hidden=hidden, depth=depth, math=mode)
     bmg = BatchMolGraph(synth.make_graphs("copolymer", batch, seed=0))
     model = MPN(bench.make_model_args(a, DEV), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)
     bench.init_weights(model)
@@ -55,10 +55,14 @@ def depth_step(mode, batch=4096):
             L.wd_debug_timing(buf, 1)
             model([bmg])
             torch.cuda.synchronize()
-    report(f"encoder forward, mode {mode} (every k_tc_gemm4 launch of one forward pass summed)")
+    report(f"encoder forward h={hidden} d={depth} B={batch}, mode {mode} (every k_tc_gemm4 launch of one forward pass summed)")
 
 
 if __name__ == "__main__":
+    if sys.argv[1:2] == ["wide"]:               # configs[3] arithmetic (h = 2400, d = 6) at 2048 graphs
+        for mode in ("tf32x3", "tf32"):
+            depth_step(mode, 2048, 2400, 6)
+        sys.exit(0)
     M = 269541
     for mode in (2, 1):
         gemm(M, 300, 147, 148, 0, mode)          # input projection (mode 1 runs k_tc_gemm3 unless rows are unaligned)
