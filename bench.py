@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument("--hidden", type=int, default=300)
     ap.add_argument("--depth", type=int, default=3)
     ap.add_argument("--kind", default="copolymer", choices=["copolymer", "qm9"])
-    ap.add_argument("--math", default=os.environ.get("WDMPNN_MATH", "tf32x3"), choices=["fp32", "tf32", "tf32x3"],
+    ap.add_argument("--math", default=os.environ.get("WDMPNN_MATH", "tf32x3"), choices=["fp32", "tf32", "tf32x3", "bf16x3"],
                     help="tf32x3 (default, the drop-in's default): tcgen05 tensor cores, error-compensated forward "
                          "contractions (encoder output <= 1e-5, predictions <= 1e-4); tf32: single pass (<= 1e-3 on the "
                          "encoder output); fp32: CUDA-core contractions")
@@ -700,7 +700,7 @@ def main():
 
     # ---- the same step in the single-pass TF32 mode (accuracy 1e-3 instead of 1e-5): what the 3xTF32 products cost -----
     single_pass = None
-    if rank == 0 and a.math == "tf32x3" and not a.no_single_pass:
+    if rank == 0 and a.math in ("tf32x3", "bf16x3") and not a.no_single_pass:
         a1 = argparse.Namespace(**vars(a))
         a1.math = "tf32"
         m1 = MPN(make_model_args(a1, dev), atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(dev)
@@ -816,7 +816,7 @@ def main():
                 "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "ms_per_step_with_events": ms_step_events,
                 "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None,
-                "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[a.math],
+                "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3", "bf16x3": "bf16x3"}[a.math],
                 "data": "synthetic",
                 "config": base_config(a, world, G, Na, Nb),
                 "options": {"math_mode": a.math, "pdl": os.environ.get("WD_PDL", "1") != "0", "sign_bits": sign_bits,

@@ -40,8 +40,12 @@ enum { WD_AGG_MEAN = 0, WD_AGG_SUM = 1, WD_AGG_NORM = 2 };
  *   TF32X3 : tcgen05.mma kind::tf32 with error compensation in the FORWARD contractions: both operands are split
  *            into tf32 hi + lo parts and a_hi w_hi + a_lo w_hi + a_hi w_lo accumulate in the same TMEM tile
  *            (fp32-grade forward: encoder output <= 1e-5, predictions <= 1e-4, the north-star bound); the backward
- *            contractions stay single-pass TF32.  The default of the Python drop-in. */
-enum { WD_MATH_FP32 = 0, WD_MATH_TF32 = 1, WD_MATH_TF32X3 = 2 };
+ *            contractions stay single-pass TF32.  The default of the Python drop-in.
+ *   BF16X3 : the same scheme with the split point at bfloat16 and every product a tcgen05.mma kind::f16: a_hi w_hi +
+ *            a_lo w_hi + a_hi w_lo over ONE bf16 image per operand (no tf32 image): 6 instead of 8 MMAs per K chunk,
+ *            half the weight bytes on the SM; forward error ~4x that of TF32X3 (encoder output <= 2e-5, predictions
+ *            <= 1e-4); backward contractions single-pass TF32 as in TF32X3. */
+enum { WD_MATH_FP32 = 0, WD_MATH_TF32 = 1, WD_MATH_TF32X3 = 2, WD_MATH_BF16X3 = 3 };
 /* WdConfig.flags */
 #define WD_FLAG_NO_SIGN_BITS 1u /* tensor-core modes, ReLU: the backward reads the stored activations instead of the  */
                                 /* 1-bit-per-element sign images the forward epilogues leave (A/B and test switch).   */

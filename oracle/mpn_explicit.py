@@ -48,6 +48,20 @@ def mm_tf32(a, b):
     return tf32_round(a) @ tf32_round(b)
 
 
+def bf16_round(x):
+    """Round-to-nearest-even of fp32 values to bfloat16 (8 significant bits): what a kind::f16 path with bf16 operands,
+    or bf16 storage of the activations, would apply."""
+    u = np.asarray(x, np.float32).view(np.uint32).astype(np.uint64)
+    u = ((u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000).astype(np.uint32)
+    return u.view(np.float32).astype(np.float64)
+
+
+def mm_bf16(a, b):
+    """Matrix product with both operands rounded to bfloat16 and exact accumulation: the error model of a single-pass
+    BF16 tensor-core mode (not built: tests/test_oracle_golden.py::test_bf16_error_model_misses_the_bound, DESIGN.md)."""
+    return bf16_round(a) @ bf16_round(b)
+
+
 def forward_backward(components, weights, d_out, depth, undirected=False,
                      aggregation="mean", aggregation_norm=100.0, mm=np.matmul):
     f_atoms, f_bonds, w_atoms, w_bonds, a2b, b2a, b2revb, a_scope, _bs, dop = components

@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("WDMPNN_LIB") or os.path.join(_HERE, "libwdmpnn.so")
 WD_OK, WD_ERR_INVALID_ARG, WD_ERR_CUDA, WD_ERR_UNSUPPORTED, WD_ERR_GRAPH = 0, -1, -2, -3, -4
 ACTIVATIONS = {"ReLU": 0, "LeakyReLU": 1, "tanh": 2, "SELU": 3, "ELU": 4}
 AGGREGATIONS = {"mean": 0, "sum": 1, "norm": 2}
-MATH_MODES = {"fp32": 0, "tf32": 1, "tf32x3": 2}
+MATH_MODES = {"fp32": 0, "tf32": 1, "tf32x3": 2, "bf16x3": 3}
 FLAG_NO_SIGN_BITS, FLAG_NO_GRAPH, FLAG_NO_SIDE_BRANCH, FLAG_NO_DEFER_SUM = 1, 2, 4, 8
 
 _f32p, _i32p, _i64p = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int64)

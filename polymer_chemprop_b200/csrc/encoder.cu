@@ -69,12 +69,14 @@ inline int adaptive_bn(int64_t rows, int N, int cap) {
   return std::min(cap, (int)round_up(ceil_div(np, n_tiles), 16));
 }
 
-inline bool is_tc(const WdConfig& c) { return c.math_mode == WD_MATH_TF32 || c.math_mode == WD_MATH_TF32X3; }
+inline bool is_tc(const WdConfig& c) {
+  return c.math_mode == WD_MATH_TF32 || c.math_mode == WD_MATH_TF32X3 || c.math_mode == WD_MATH_BF16X3;
+}
 
 Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool infer = false) {
   Layout L;
   const int h = c.hidden_size;
-  const bool tc = is_tc(c), x3 = c.math_mode == WD_MATH_TF32X3;
+  const bool tc = is_tc(c), bx3 = c.math_mode == WD_MATH_BF16X3, x3 = c.math_mode == WD_MATH_TF32X3 || bx3;
   L.tc = tc;
   L.ldh = (int)round_up(h, 8);   // rows start on 32-byte sectors: a 128-byte row chunk is exactly 4 sectors
   L.szB = round_up(Nb * L.ldh, 64);
@@ -113,10 +115,11 @@ Layout make_layout(const WdConfig& c, int64_t Na, int64_t Nb, int64_t G, bool in
   L.partials = L.Po;
   // forward weights: the 3xTF32 mode runs all three contractions on k_tc_gemm4 (tiles up to 304 columns, hi + lo
   // images); the single-pass mode keeps the plain ones on the TMA-fed k_tc_gemm3 (tiles up to 160 columns)
-  const int fwd_bn = x3 ? T4_MAX_BN : T2_MAX_BN, parts = x3 ? 2 : 1;
-  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0, adaptive_bn(Nb, h, fwd_bn), parts);     // I = f_bonds W_i^T
-  L.pWh = tc_packed_geometry(h, h, 0, adaptive_bn(Nb, h, T4_MAX_BN), parts);            // S W_h^T (gathered depth step)
-  L.pWo = tc_packed_geometry(h, c.atom_fdim, h, adaptive_bn(Na, h, fwd_bn), parts);     // [f_atoms, A_d] W_o^T
+  // (3xBF16: the same kernel and tiles with ONE bf16 hi | lo image per chunk, tc_gemm4.cuh)
+  const int fwd_bn = x3 ? T4_MAX_BN : T2_MAX_BN, parts = x3 && !bx3 ? 2 : 1, bf = bx3 ? 1 : 0;
+  L.pWi = tc_packed_geometry(h, c.bond_fdim, 0, adaptive_bn(Nb, h, fwd_bn), parts, bf);     // I = f_bonds W_i^T
+  L.pWh = tc_packed_geometry(h, h, 0, adaptive_bn(Nb, h, T4_MAX_BN), parts, bf);            // S W_h^T (gathered depth step)
+  L.pWo = tc_packed_geometry(h, c.atom_fdim, h, adaptive_bn(Na, h, fwd_bn), parts, bf);     // [f_atoms, A_d] W_o^T
   L.pWhT = tc_packed_geometry(h, h, 0, adaptive_bn(Nb, h, T2_MAX_BN));   // dS = dZ W_h     (backward: single-pass TF32 in both modes)
   L.pWoT = tc_packed_geometry(h, h, 0, adaptive_bn(Na, h, T2_MAX_BN));   // dA_d = dZo W_o[:, F_a:]
   // the message gradient only needs (y > 0) of a ReLU output: the tensor-core epilogues leave those bits behind
@@ -139,7 +142,8 @@ int check_cfg(const WdConfig* c) {
     return fail(WD_ERR_UNSUPPORTED, "activation %d not supported (ReLU, LeakyReLU, tanh, SELU, ELU)", c->activation);
   if (c->aggregation < WD_AGG_MEAN || c->aggregation > WD_AGG_NORM)
     return fail(WD_ERR_INVALID_ARG, "aggregation %d unknown", c->aggregation);
-  if (c->math_mode != WD_MATH_FP32 && c->math_mode != WD_MATH_TF32 && c->math_mode != WD_MATH_TF32X3)
+  if (c->math_mode != WD_MATH_FP32 && c->math_mode != WD_MATH_TF32 && c->math_mode != WD_MATH_TF32X3 &&
+      c->math_mode != WD_MATH_BF16X3)
     return fail(WD_ERR_INVALID_ARG, "math_mode %d unknown", c->math_mode);
   if (!(c->dropout >= 0.f && c->dropout < 1.f))
     return fail(WD_ERR_INVALID_ARG, "dropout %g must be in [0, 1)", (double)c->dropout);
@@ -755,8 +759,8 @@ extern "C" int wd_debug_gemm(const float* A, int lda, const float* W, int ldb, i
   WdConfig c{};
   c.math_mode = math_mode;
   // TF32X3: the forward kernel's geometry (tiles up to 304 columns, hi + lo weight images); b_kn is a backward form
-  const bool x3 = math_mode == WD_MATH_TF32X3 && !b_kn;
-  TcPacked pk = tc_packed_geometry(N, K, 0, x3 ? T4_MAX_BN : T2_MAX_BN, x3 ? 2 : 1);
+  const bool bx3 = math_mode == WD_MATH_BF16X3 && !b_kn, x3 = (math_mode == WD_MATH_TF32X3 && !b_kn) || bx3;
+  TcPacked pk = tc_packed_geometry(N, K, 0, x3 ? T4_MAX_BN : T2_MAX_BN, x3 && !bx3 ? 2 : 1, bx3 ? 1 : 0);
   if (math_mode != WD_MATH_FP32) {
     if (!scratch || scratch_bytes < (size_t)pk.floats() * sizeof(float))
       return fail(WD_ERR_INVALID_ARG, "wd_debug_gemm: scratch needs %lld bytes", (long long)pk.floats() * 4);

@@ -61,12 +61,15 @@ inline TcTiling tc_tiling(int N, int max_bn) {
 // concatenation of two segments (K1, K2), each padded to a multiple of 32.
 // parts == 2 (3xTF32, math mode TF32X3): every (n_tile, k_chunk) holds TWO images back to back: hi = tf32(w), and the
 //   bf16 CORRECTION image whose 128-byte rows are [bf16(hi) (k = 0..31) | bf16(w - hi) (k = 0..31)] (tc_gemm4.cuh).
+// bf == 1 (3xBF16, math mode BF16X3; parts == 1): ONE image per (n_tile, k_chunk) in the correction-image format with the
+//   split point at bfloat16: rows [bf16(w) | bf16(w - bf16(w))].
 // ---------------------------------------------------------------------------------------------
 struct TcPackJob {
   const float* W;
   int ldb, bmode, N, K1, K2, BN, n_tiles, KC1, KC, parts;
   float* Bp;
   int64_t first;     // index of this job's first element in the launch (jobs are laid end to end)
+  int bf;            // 1: the single image is the bf16 hi | lo image of the 3xBF16 mode
 };
 struct TcPackJobs {  // up to three weight matrices packed by ONE launch (forward: W_i, W_h, W_o; backward: W_h^T, W_o^T)
   TcPackJob job[3];
@@ -99,9 +102,9 @@ __global__ void k_tc_pack_b(const TcPackJobs jobs) {
   else          { int k = (kc - KC1) * 32 + kk; if (k < K2) kglob = K1 + k; }
   float v = 0.f;
   if (n < N && kglob >= 0) v = bmode == B_NK ? __ldg(W + (int64_t)n * ldb + kglob) : __ldg(W + (int64_t)kglob * ldb + n);
-  const float hi = ptx::to_tf32(v);
+  const float hi = j.bf ? __uint_as_float(ptx::pack_bf16(v, 0.f) << 16) : ptx::to_tf32(v);
   const int64_t img = (((int64_t)nt * KC + kc) * parts + part) * BN * 32;
-  if (part == 0) {
+  if (part == 0 && !j.bf) {
     Bp[img + (ptx::sw128_off(nl, kk >> 2) >> 2) + (kk & 3)] = hi;
   } else {   // bf16 element j of the row sits in 16-byte chunk j / 8: j = kk (hi) and j = 32 + kk (lo)
     uint16_t* row = reinterpret_cast<uint16_t*>(Bp + img);

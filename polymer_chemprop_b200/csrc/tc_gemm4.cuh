@@ -37,6 +37,15 @@
 // not by the weight traffic.  No extra HBM pass: the correction image of A is written over the subtrahend part of
 // the SAME smem stage (after a named barrier among the transform warps when that part holds the shared TMA box);
 // the weight ring streams two images per chunk from L2.
+// 3xBF16 (T4Params.split == 2, math mode WD_MATH_BF16X3): the same correction images with the split point at bfloat16,
+//   a = a_hi + a_lo, a_hi = bf16(a), a_lo = bf16(a - a_hi);  w likewise;  a w ~= a_hi w_hi + a_lo w_hi + a_hi w_lo
+// (dropped: ~2^-17 of the product; the exact-accumulation model gives 3e-6 on the encoder output at h = 300 against 4e-7 for
+// 3xTF32 and 2e-4 for single-pass TF32, tests/test_oracle_golden.py).  There is NO tf32 image: the operand stage holds
+// the raw rows and ONE 128-byte-row image [a_lo | a_hi], the weight ring one image [w_hi | w_lo] per chunk, and a K chunk
+// is six kind::f16 MMAs per accumulator half -- the four of the correction group (a_lo w_hi + a_hi w_lo over the 64
+// bf16 of a row) plus two that pair the a_hi half of the operand row with the w_hi half of the weight row (descriptor
+// start addresses 64 bytes apart).  Against 3xTF32: 6 instead of 8 MMAs, half the weight-ring bytes, no hi-image write
+// -- ~28 % fewer bytes through the shared-memory port, which is what bounds this kernel (profiles/r2_fwd_abl.log, L).
 //   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 operand loaders, 11-14 transform,
 //   15-18 second epilogue group.
 #pragma once
@@ -114,7 +123,8 @@ struct T4Params {
   SignBits sign;        // (stored value > 0) bits, written next to C when sign.p != nullptr
   int x1_tma;           // GATHER: 1: i1(r) == ((r-1)^1)+1 for every r >= 1 (adjacent reverse pairs): X1 rows arrive by TMA
   int a_tma;            // PLAIN: 1: rows are 16-byte aligned and arrive by TMA; 0: 4-byte cp.async copies
-  int split;            // 1: 3xTF32 (hi / lo operand images, three MMAs per K step); 0: single-pass TF32
+  int split;            // 0: single-pass TF32; 1: 3xTF32 (tf32 hi image + bf16 correction image, two MMA groups per K chunk);
+                        // 2: 3xBF16 (ONE bf16 [lo | hi] image per operand, three bf16 products per K chunk, see below)
   CUtensorMap mb[2];    // CTA pair: the packed weight images as one [rows, 32] matrix, box = (W0 / 2, W1 / 2) rows, no swizzle
 };
 
@@ -300,7 +310,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
   // The weight ring holds T4_B_STAGES chunk images [BN x 128 bytes]; it is filled and drained in UNITS of one
   // accumulator half of one image (hi, then lo when split), each unit with its own full / empty barrier: unit u
   // lives in slot u % (2 nh) = (stage, half).
-  const int nh = W1 > 0 ? 2 : 1, parts = p.split ? 2 : 1, nslots = B_STAGES * nh;
+  const int nh = W1 > 0 ? 2 : 1, parts = p.split == 1 ? 2 : 1, nslots = B_STAGES * nh;
   const int h1_off = PAIR ? W0 * 64 : W0 * 128;                        // where the second half's unit starts inside a stage
 
   if (warp >= T4_XFORM_W0 && warp < T4_EPI2_W0) {
@@ -349,6 +359,16 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
           if (GATHER) {
             if (PREACT) u[j] = f4_act<ACT>(u[j]);
             v[j] = make_float4(v[j].x - u[j].x, v[j].y - u[j].y, v[j].z - u[j].z, v[j].w - u[j].w);
+          }
+          if (p.split == 2) {   // 3xBF16: one image, [a_lo | a_hi] with a_hi = bf16(a); the raw rows stay as they are
+            const uint32_t h01 = ptx::pack_bf16(v[j].x, v[j].y), h23 = ptx::pack_bf16(v[j].z, v[j].w);
+            const float4 hi = make_float4(__uint_as_float(h01 << 16), __uint_as_float(h01 & 0xffff0000u),
+                                          __uint_as_float(h23 << 16), __uint_as_float(h23 & 0xffff0000u));
+            uint8_t* row = x1 + (rb + T4_XR * j) * 128 + (c & 1) * 8;
+            *reinterpret_cast<uint2*>(row + (((c >> 1) ^ (rb & 7)) << 4)) =
+                make_uint2(ptx::pack_bf16(v[j].x - hi.x, v[j].y - hi.y), ptx::pack_bf16(v[j].z - hi.z, v[j].w - hi.w));
+            *reinterpret_cast<uint2*>(row + (((4 + (c >> 1)) ^ (rb & 7)) << 4)) = make_uint2(h01, h23);
+            continue;
           }
           const float4 hi = make_float4(ptx::to_tf32(v[j].x), ptx::to_tf32(v[j].y), ptx::to_tf32(v[j].z), ptx::to_tf32(v[j].w));
           *reinterpret_cast<float4*>(st + j * (T4_XR * 128)) = hi;
@@ -576,7 +596,20 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
           }
           ptx::tc_fence_after();
           // issued from convergent code, the election is inside each statement (tc_ptx.cuh: mma_elect)
-          if (part == 0) {
+          if (p.split == 2) {       // 3xBF16: a_lo w_hi + a_hi w_lo (the row's 64 bf16), then a_hi w_hi (row halves paired crosswise)
+#pragma unroll
+            for (int ks = 0; ks < 6; ++ks)
+              for (int hb = 0; hb < nh; ++hb) {
+                const uint32_t ao = ks < 4 ? 2 * ks : 4 + 2 * (ks - 4), bo = ks < 4 ? 2 * ks : 2 * (ks - 4);
+                const uint32_t acc = (kc == 0 && ks == 0) ? 0u : 1u;
+                if (WD_ABL & 128) {
+                } else if (PAIR) {
+                  ptx::mma_elect_pair<true>(d[hb], a_lo_lo + ao, b_addr[hb] + bo, ptx::kDescHiSw128, idc[hb], acc);
+                } else {
+                  ptx::mma_elect<true>(d[hb], a_lo_lo + ao, b_addr[hb] + bo, ptx::kDescHiSw128, idc[hb], acc);
+                }
+              }
+          } else if (part == 0) {
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
               for (int hb = 0; hb < nh; ++hb)

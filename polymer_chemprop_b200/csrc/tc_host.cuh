@@ -15,13 +15,14 @@ struct TcPacked {
   int N, K1, K2, BN, n_tiles, KC1, KC;
   int parts;   // 1: tf32(w); 2: hi and lo images per (column tile, K chunk) for the 3xTF32 kernels
   float* img;
+  int bf = 0;  // 1 (with parts == 1): the image is the bf16 [hi | lo] image of the 3xBF16 kernels (tc_core.cuh)
   int64_t floats() const { return (int64_t)n_tiles * KC * BN * 32 * parts; }
 };
 
 // max_bn: widest column tile the consuming kernel takes (160: k_tc_gemm3's two TMEM accumulators; 304: k_tc_gemm4)
-inline TcPacked tc_packed_geometry(int N, int K1, int K2, int max_bn = T2_MAX_BN, int parts = 1) {
+inline TcPacked tc_packed_geometry(int N, int K1, int K2, int max_bn = T2_MAX_BN, int parts = 1, int bf = 0) {
   const TcTiling t = tc_tiling(N, max_bn);
-  TcPacked g{N, K1, K2, t.BN, t.n_tiles, (int)ceil_div(K1, TC_BK), 0, parts, nullptr};
+  TcPacked g{N, K1, K2, t.BN, t.n_tiles, (int)ceil_div(K1, TC_BK), 0, parts, nullptr, bf};
   g.KC = g.KC1 + (int)ceil_div(K2, TC_BK);
   return g;
 }
@@ -31,7 +32,7 @@ struct TcPacker {
   TcPackJobs jobs{};
   void add(const float* W, int ldb, int bmode, const TcPacked& g) {
     TcPackJob& j = jobs.job[jobs.n++];
-    j = TcPackJob{W, ldb, bmode, g.N, g.K1, g.K2, g.BN, g.n_tiles, g.KC1, g.KC, g.parts, g.img, jobs.total};
+    j = TcPackJob{W, ldb, bmode, g.N, g.K1, g.K2, g.BN, g.n_tiles, g.KC1, g.KC, g.parts, g.img, jobs.total, g.bf};
     jobs.total += g.floats();
   }
   int run(cudaStream_t s) {
@@ -76,7 +77,7 @@ int tc_gemm4(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   T4Params p{};
   p.drop = drop;
   p.sign = sign;
-  p.split = B.parts == 2 ? 1 : 0;
+  p.split = B.bf ? 2 : (B.parts == 2 ? 1 : 0);
   if (B.BN > T4_MAX_BN) return fail(WD_ERR_UNSUPPORTED, "tcgen05 forward kernel: unsupported tile geometry");
   if (!tc_aligned16(C, ldc)) return fail(WD_ERR_INVALID_ARG, "tcgen05 output rows must be 16-byte aligned");
   int rc = WD_OK;
@@ -169,7 +170,7 @@ int tc_gemm3(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* 
   return WD_OK;
 }
 
-// C[M, ldc] = epi( A[M, K1+K2] * B^T ) with B packed.  B.parts == 2 selects the 3xTF32 kernel.
+// C[M, ldc] = epi( A[M, K1+K2] * B^T ) with B packed.  B.parts == 2 selects the 3xTF32 kernel, B.bf the 3xBF16 form of it.
 template <int AMODE, int EPI, int ACT, bool PREACT>
 int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* bias, const float* R, int ldr,
             float* C, int ldc, int64_t M, const Dropout& drop = Dropout{}, const SignBits& sign = SignBits{}) {
@@ -177,7 +178,7 @@ int tc_gemm(cudaStream_t s, const AOperand& A, const TcPacked& B, const float* b
     return tc_gemm4<AMODE, EPI, ACT, PREACT>(s, A, B, bias, R, ldr, C, ldc, M, drop, sign);
   } else {
     const bool aligned = tc_aligned16(A.X, A.ldx) && tc_aligned16(C, ldc) && (AMODE != A_CONCAT || tc_aligned16(A.X2, A.ldx2));
-    if (B.parts == 1 && B.BN <= T2_MAX_BN && aligned) return tc_gemm3<AMODE, EPI, ACT>(s, A, B, bias, C, ldc, M, drop, sign);
+    if (B.parts == 1 && !B.bf && B.BN <= T2_MAX_BN && aligned) return tc_gemm3<AMODE, EPI, ACT>(s, A, B, bias, C, ldc, M, drop, sign);
     return tc_gemm4<AMODE, EPI, ACT, false>(s, A, B, bias, R, ldr, C, ldc, M, drop, sign);
   }
 }

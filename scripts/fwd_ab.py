@@ -60,11 +60,11 @@ if __name__ == "__main__":
     tag = os.path.basename(os.environ.get("WDMPNN_LIB", "libwdmpnn.so"))
     M = 269541
     res = [f"{tag}:"]
-    for mode in (2, 1):
+    for mode in (2, 1, 3):
         res.append(f"gemm K=147 store m{mode} {gemm(M, 300, 147, 148, 0, mode):.0f}us")
         res.append(f"gemm K=300 res m{mode} {gemm(M, 300, 300, 304, 2, mode):.0f}us")
     bmg = BatchMolGraph(synth.make_graphs("copolymer", 4096, seed=0))
-    for mode in ("tf32x3", "tf32"):
+    for mode in ("tf32x3", "tf32", "bf16x3"):
         f, s = encoder(mode, bmg)
         res.append(f"{mode} fwd {f:.0f}us step {s:.0f}us")
     print(" | ".join(res), flush=True)

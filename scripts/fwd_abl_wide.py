@@ -32,7 +32,7 @@ if __name__ == "__main__":
     tag = os.path.basename(os.environ.get("WDMPNN_LIB", "libwdmpnn.so"))
     bmg = BatchMolGraph(synth.make_graphs("copolymer", batch, seed=0))
     out = [f"{tag} h={hidden} d={depth} B={batch}:"]
-    for mode in ("tf32x3", "tf32"):
+    for mode in ("tf32x3", "tf32", "bf16x3"):
         t = {}
         for d in (depth, 2):
             a = types.SimpleNamespace(hidden=hidden, depth=d, math=mode)

@@ -96,7 +96,10 @@ def dropout_case(math_mode, hidden, depth, activation, p, out_tol, grad_tol):
 # TF32 on exact activations (no ReLU-mask flips), hence the tighter gradient bound than plain tf32.
 TOL = {"fp32": dict(out=1e-5, grad=1e-4, gemm=1e-5),
        "tf32": dict(out=1e-3, grad=3e-2, gemm=1e-3),
-       "tf32x3": dict(out=1e-5, grad=5e-3, gemm=5e-6)}
+       "tf32x3": dict(out=1e-5, grad=5e-3, gemm=5e-6),
+       # bf16x3: the same three products with the split point at bfloat16 (2^-17 dropped instead of 2^-22): the
+       # exact-accumulation model gives 3e-6 on the encoder output (tests/test_oracle_golden.py)
+       "bf16x3": dict(out=2e-5, grad=5e-3, gemm=2e-5)}
 
 
 def record(key, **values):

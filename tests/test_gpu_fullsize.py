@@ -28,11 +28,13 @@ pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda", 0)
 FULL_TOL = {"fp32": dict(out=1e-5, out_max=2e-4, grad=1e-3),
             "tf32x3": dict(out=1e-5, out_max=2e-4, grad=2e-3),
+            "bf16x3": dict(out=2e-5, out_max=4e-4, grad=2e-3),
             "tf32": dict(out=1e-3, out_max=2e-2, grad=3e-2)}
 WIDE_TOL = {"fp32": dict(out=1e-5, out_max=2e-4, grad=1e-3),          # h = 2400, d = 6, 48 graphs
             "tf32x3": dict(out=1e-4, out_max=2e-3, grad=5e-3),
+            "bf16x3": dict(out=1e-4, out_max=2e-3, grad=5e-3),
             "tf32": dict(out=1e-3, out_max=2e-2, grad=3e-2)}
-MODES = ["fp32", "tf32x3", "tf32"]
+MODES = ["fp32", "tf32x3", "bf16x3", "tf32"]
 
 
 def _weights(h, fa, fb, seed=0):

@@ -52,7 +52,7 @@ class Model(nn.Module):
 
 
 @pytest.mark.parametrize("name", NAMES)
-@pytest.mark.parametrize("mode,pred_tol,grad_tol", [("fp32", 1e-5, 1e-4), ("tf32x3", 1e-4, 5e-3), ("tf32", 1e-3, 3e-2)])
+@pytest.mark.parametrize("mode,pred_tol,grad_tol", [("fp32", 1e-5, 1e-4), ("tf32x3", 1e-4, 5e-3), ("bf16x3", 1e-4, 5e-3), ("tf32", 1e-3, 3e-2)])
 def test_full_model_predictions_and_gradients_match_reference(name, mode, pred_tol, grad_tol):
     """The default mode is the one that must meet the north star: MPN(args) without wd_math_mode."""
     z = np.load(os.path.join(MODEL_DIR, name + ".npz"))

@@ -231,7 +231,7 @@ def test_inference_path_equals_training_forward_bitwise():
     """torch.no_grad() -> wd_encoder_infer (predict.py:10-68): same kernels, smaller workspace, same bits."""
     import ctypes as C
     bmg = BatchMolGraph(synth.make_graphs("copolymer", 300, 41) + [synth.empty_graph()])
-    for mode in ("fp32", "tf32", "tf32x3"):
+    for mode in ("fp32", "tf32", "tf32x3", "bf16x3"):
         torch.manual_seed(3)
         model = _util.MPN(_util.make_args(hidden_size=300, depth=4, wd_math_mode=mode), atom_fdim=bmg.atom_fdim,
                           bond_fdim=bmg.bond_fdim).to(DEV)
@@ -260,7 +260,7 @@ def _star_graph(rng, n_leaves):
     return synth._assemble(n, pairs, w, fa, fb, rng.uniform(0.2, 1.0, n).astype(np.float32), 1.0 + float(rng.uniform(1, 3)))
 
 
-@pytest.mark.parametrize("mode,out_tol,grad_tol", [("fp32", OUT_TOL, GRAD_TOL), ("tf32x3", 1e-5, 5e-3), ("tf32", 1e-3, 3e-2)])
+@pytest.mark.parametrize("mode,out_tol,grad_tol", [("fp32", OUT_TOL, GRAD_TOL), ("tf32x3", 1e-5, 5e-3), ("bf16x3", 2e-5, 5e-3), ("tf32", 1e-3, 3e-2)])
 @pytest.mark.parametrize("case", ["depth1", "star_k40", "one_molecule_h8"])
 def test_edge_shapes_match_oracle(case, mode, out_tol, grad_tol):
     """Edges of the shape space: depth 1 (no message passing, W_h unused: the reference leaves its grad None),

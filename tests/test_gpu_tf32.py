@@ -5,6 +5,8 @@ Two tensor-core math modes (include/wdmpnn.h), tolerances in tests/_util.py TOL:
 * tf32x3 (the default of the drop-in): error-compensated forward contractions (a_hi w_hi + a_lo w_hi + a_hi w_lo in
   one TMEM accumulator) -- encoder output <= 1e-5 relative like the FP32 path, raw contraction <= 5e-6; the backward
   contractions are single-pass TF32 on exact activations: gradients <= 5e-3 on the tiny golden batches.
+* bf16x3: the same three products with the split point at bfloat16, every MMA kind::f16 (csrc/tc_gemm4.cuh): encoder
+  output <= 2e-5, raw contraction <= 2e-5, gradients as tf32x3.
 * tf32 (single pass): BASELINE.json's <= 1e-3 relative on the encoder output (||x-ref||_F / ||ref||_F).  Gradients
   are held to 3e-2: an exact-accumulation TF32 model of the reference (oracle/mpn_explicit.py mm_tf32,
   tests/test_oracle_golden.py::test_tf32_error_model) already shows up to 2e-2 on these tiny batches, because 3e-4
@@ -20,8 +22,8 @@ from polymer_chemprop_b200 import BatchMolGraph, _capi, synth
 
 pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda", 0)
-MODES = ["tf32", "tf32x3"]
-MODE_ID = {"tf32": 1, "tf32x3": 2}
+MODES = ["tf32", "tf32x3", "bf16x3"]
+MODE_ID = {"tf32": 1, "tf32x3": 2, "bf16x3": 3}
 TOL = _util.TOL
 
 
@@ -255,7 +257,7 @@ def test_sign_bits_give_the_same_gradients_as_the_stored_activations_bitwise(hid
         assert torch.equal(res["1"][1][k], res["0"][1][k]), k
 
 
-@pytest.mark.parametrize("mode", ["tf32x3", "tf32"])
+@pytest.mark.parametrize("mode", ["tf32x3", "tf32", "bf16x3"])
 def test_cta_pair_kernel_gives_the_same_bits_as_the_single_cta_kernel(mode, monkeypatch):
     """WD_T4_PAIR=1 runs the forward contractions as clusters of two CTAs (tcgen05.mma.cta_group::2: one M = 256 MMA
     per pair, each CTA holding half of every weight unit; csrc/tc_gemm4.cuh).  Same products accumulated in the same
