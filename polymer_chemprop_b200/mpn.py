@@ -437,10 +437,13 @@ class MPNEncoder(nn.Module):
 
 
 def _default_math_mode() -> str:
-    """tf32x3: tcgen05 tensor cores with error-compensated (3xTF32) forward contractions -- fp32-grade encoder output
-    and predictions (<= 1e-4, the bound BASELINE.json states for a tensor-core path) at tensor-core speed.
-    WDMPNN_MATH=tf32 (single pass, ~5e-4 on predictions) or fp32 (CUDA cores) select the other modes."""
-    return os.environ.get("WDMPNN_MATH", "tf32x3")
+    """bf16x3: tcgen05 tensor cores with error-compensated forward contractions, operands split at bfloat16 and three
+    kind::f16 products per element (a_hi w_hi + a_lo w_hi + a_hi w_lo, fp32 accumulation in TMEM) -- encoder output
+    4e-6 .. 6e-6 at h=300, predictions <= 2e-5 (the bound BASELINE.json states for a tensor-core path is 1e-4), and the
+    fastest of the modes (fewer bytes through shared memory than single-pass TF32 needs).
+    WDMPNN_MATH=tf32x3 (split at TF32: 2e-6), tf32 (single pass, ~5e-4 on predictions) or fp32 (CUDA cores) select the
+    other modes."""
+    return os.environ.get("WDMPNN_MATH", "bf16x3")
 
 
 class MPN(nn.Module):

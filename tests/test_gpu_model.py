@@ -94,4 +94,4 @@ def test_default_math_mode_is_the_error_compensated_tensor_core_mode(monkeypatch
     monkeypatch.delenv("WDMPNN_MATH", raising=False)
     args = _util.make_args()
     del args.wd_math_mode
-    assert MPN(args).encoder[0].math_mode == "tf32x3"
+    assert MPN(args).encoder[0].math_mode == "bf16x3"
