@@ -14,7 +14,7 @@ DEV = torch.device("cuda", 0)
 bmg = BatchMolGraph(synth.make_graphs("copolymer", 300, 61, random_edge_weights=True) + [synth.empty_graph()] +
                     synth.make_graphs("qm9", 50, 62))
 total_bad = 0
-for mode, depth, und, bias in (("tf32x3", 3, False, False), ("tf32x3", 4, False, True), ("tf32", 5, True, False), ("fp32", 3, True, True)):
+for mode, depth, und, bias in (("bf16x3", 3, False, False), ("bf16x3", 5, True, True), ("tf32x3", 3, False, False), ("tf32x3", 4, False, True), ("tf32", 5, True, False), ("fp32", 3, True, True)):
     torch.manual_seed(1)
     model = _util.MPN(_util.make_args(hidden_size=300, depth=depth, undirected=und, bias=bias, wd_math_mode=mode),
                       atom_fdim=bmg.atom_fdim, bond_fdim=bmg.bond_fdim).to(DEV)

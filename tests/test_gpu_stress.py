@@ -13,7 +13,8 @@ pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda", 0)
 
 
-@pytest.mark.parametrize("mode,depth,undirected,bias", [("tf32x3", 3, False, False), ("tf32x3", 4, False, True),
+@pytest.mark.parametrize("mode,depth,undirected,bias", [("bf16x3", 3, False, False), ("bf16x3", 4, True, True),
+                                                        ("tf32x3", 3, False, False), ("tf32x3", 4, False, True),
                                                         ("tf32", 5, True, False)])
 def test_forty_steps_in_a_row_give_the_same_bits_with_and_without_the_side_branch(mode, depth, undirected, bias, monkeypatch):
     bmg = BatchMolGraph(synth.make_graphs("copolymer", 300, 61, random_edge_weights=True) + [synth.empty_graph()] +
