@@ -62,10 +62,22 @@ inline int t3_smem_bytes(int BN) {
 template <int EPI, int ACT>
 __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, uint32_t& rit, int BN,
                                             int64_t row0, int64_t M, int col0, int N, int cmax, const float* bias,
-                                            float* C, int ldc, const Dropout& drop, const SignBits& sign, int grp) {
+                                            float* C, int ldc, const Dropout& drop, const SignBits& sign, int grp,
+                                            uint64_t* tmem_empty) {
   uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
   const int rows_ok = (int)min((int64_t)32, M - (row0 + we * 32));         // rows of this warp inside the matrix (may be <= 0)
   const uint32_t rit0 = rit;
+  // the accumulator goes back to the MMA warp right after this warp's last tcgen05.ld of the tile (tc_gemm4.cuh: t4_epilogue)
+  auto release = [&]() {
+    ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(tmem_empty);
+  };
+  const uint32_t nch = (uint32_t)((BN + 31) >> 5);
+  uint32_t last = rit0 + nch - 1u;
+  bool has_chunk = true;
+  if (T3_EPI_GROUPS > 1 && (int)(last & 1u) != grp) { has_chunk = nch >= 2u; last -= 1u; }
+  if (!has_chunk) release();
   for (int c0 = 0; c0 < BN; c0 += 32, ++rit) {
     if (T3_EPI_GROUPS > 1 && (int)(rit & 1u) != grp) continue;             // the other group's chunk
     const int slot = T3_EPI_GROUPS > 1 ? grp : (int)(rit % T2_R_SLOTS);     // staging only: one slot per group
@@ -80,6 +92,7 @@ __device__ __forceinline__ void t3_epilogue(uint32_t tmem_acc, int we, int lane,
       for (int j = 16; j < 32; ++j) v[j] = 0.f;
     }
     ptx::tmem_ld_wait();
+    if (has_chunk && rit == last) release();
     float4* myrow = reinterpret_cast<float4*>(sl + lane * T2_R_ROW);
 #pragma unroll
     for (int j = 0; j < 8; ++j) myrow[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -193,10 +206,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_tc_gemm3(const __grid_constan
       T2_WAIT(7, &bar->tmem_full[acc], (tl >> 1) & 1);
       ptx::tc_fence_after();
       t3_epilogue<EPI, ACT>(tmem_base + acc * 256, wq, lane, rring, rit, p.BN, row0, p.M, col0, p.N, p.ldc, p.bias,
-                            p.C, p.ldc, p.drop, p.sign, grp);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&bar->tmem_empty[acc]);
+                            p.C, p.ldc, p.drop, p.sign, grp, &bar->tmem_empty[acc]);
     }
   }
 #ifdef WD_T2_TIMING

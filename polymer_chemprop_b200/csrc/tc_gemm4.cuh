@@ -148,14 +148,29 @@ __device__ __forceinline__ uint32_t t4_rfull_parity(uint32_t rit) {
 // accumulator row to the residual chunk in the (swizzled) ring slot (EPI == E_RES_ACT; otherwise the slot is only the
 // transpose staging of this warp's 32 rows), then the warp writes the 32 rows out with 16-byte stores (8 lanes per
 // row), applying bias + activation.
-template <int EPI, int ACT>
+// The accumulator buffer is handed back to the MMA warp (`tmem_empty`) as soon as this warp's LAST tcgen05.ld of the half
+// has completed -- the rest of that chunk (staging, activation, stores) works from registers.  (The MMA warp waited 29-33 %
+// of the kernel for a free accumulator with the hand-back after the stores: profiles/r2_n_fwd_timing.log.)
+template <int EPI, int ACT, bool PAIR>
 __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane, uint8_t* rring, T4Barriers* bar,
                                             uint32_t& rit, int W, int64_t row0, int64_t M, int col0, int N, int cmax,
                                             const float* bias, float* C, int ldc, long long* tacc,
-                                            const Dropout& drop, const SignBits& sign, int sign_tile, int grp) {
+                                            const Dropout& drop, const SignBits& sign, int sign_tile, int grp,
+                                            uint64_t* tmem_empty) {
   uint32_t sw[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // sign words of this lane's chunk (common.cuh: sign_collect)
   const int rows_ok = (int)min((int64_t)32, M - (row0 + we * 32));        // rows of this warp inside the matrix (may be <= 0)
   const uint32_t rit0 = rit;
+  auto release = [&]() {
+    ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(tmem_empty); else ptx::mbar_arrive(tmem_empty); }
+  };
+  // this group's last chunk of the half (chunk numbers rit0 .. rit0 + nch - 1, a group takes those of its parity)
+  const uint32_t nch = (uint32_t)((W + 31) >> 5);
+  uint32_t last = rit0 + nch - 1u;
+  bool has_chunk = true;
+  if (T4_EPI_GROUPS > 1 && (int)(last & 1u) != grp) { has_chunk = nch >= 2u; last -= 1u; }
+  if (!has_chunk) release();                       // nothing to read for this group: hand back at once
   for (int c0 = 0; c0 < W; c0 += 32, ++rit) {
     if (T4_EPI_GROUPS > 1 && (int)(rit & 1u) != grp) continue;            // the other group's chunk
     // the residual's ring slot (handed over chunk by chunk through r_full / r_empty); without a residual the slot is
@@ -168,6 +183,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bar->r_empty[slot]);
       }
+      if (has_chunk && rit == last) release();
       continue;
     }
     float v[32];
@@ -181,6 +197,7 @@ __device__ __forceinline__ void t4_epilogue(uint32_t tmem_acc, int we, int lane,
     }
     if (EPI == E_RES_ACT) T2_WAIT(8, &bar->r_full[t4_rfull(rit)], t4_rfull_parity(rit));
     ptx::tmem_ld_wait();
+    if (has_chunk && rit == last) release();
     uint8_t* myrow = sl + lane * 128;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -662,12 +679,10 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
         const int buf = g % 3;
         T2_WAIT(7, &bar->tmem_full[buf], (g / 3) & 1);
         ptx::tc_fence_after();
-        t4_epilogue<EPI, ACT>(tmem_base + buf * T4_HALF, wq, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
-                              col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop, p.sign,
-                              (int)(tile % p.n_tiles) * p.sign.tpn + hb, grp);
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&bar->tmem_empty[buf]); else ptx::mbar_arrive(&bar->tmem_empty[buf]); }
+        // (the accumulator is handed back inside, after the warp's last tcgen05.ld of the half)
+        t4_epilogue<EPI, ACT, PAIR>(tmem_base + buf * T4_HALF, wq, lane, rring, bar, rit, hb == 0 ? W0 : W1, row0, p.M,
+                                    col0 + hb * W0, p.N, p.ldc, p.bias, p.C, p.ldc, tacc, p.drop, p.sign,
+                                    (int)(tile % p.n_tiles) * p.sign.tpn + hb, grp, &bar->tmem_empty[buf]);
       }
     }
   }

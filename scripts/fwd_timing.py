@@ -60,12 +60,12 @@ def depth_step(mode, batch=4096, hidden=300, depth=3):
 
 if __name__ == "__main__":
     if sys.argv[1:2] == ["wide"]:               # configs[3] arithmetic (h = 2400, d = 6) at 2048 graphs
-        for mode in ("tf32x3", "tf32"):
+        for mode in ("bf16x3", "tf32x3", "tf32"):
             depth_step(mode, 2048, 2400, 6)
         sys.exit(0)
     M = 269541
-    for mode in (2, 1):
+    for mode in (3, 2, 1):
         gemm(M, 300, 147, 148, 0, mode)          # input projection (mode 1 runs k_tc_gemm3 unless rows are unaligned)
         gemm(M, 300, 300, 304, 2, mode)          # residual epilogue through k_tc_gemm4, plain operand
-    for mode in ("tf32x3", "tf32"):
+    for mode in ("bf16x3", "tf32x3", "tf32"):
         depth_step(mode)

@@ -23,4 +23,4 @@ for f in ("bench", "bench_b50", "bench_ref"):
 PY
 CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-small-batch --no-single-pass"
 echo "== ncu launch list"; $CMD > gpurun_out/ncu_plain.log 2>&1 && \
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_n_ncu_launches.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "list rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_o_ncu_launches.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "list rc=$?"
