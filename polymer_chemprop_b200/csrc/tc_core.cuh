@@ -22,7 +22,8 @@ constexpr int TC_SMEM_LIMIT = 227 * 1024;
 #ifndef WD_ABL
 #define WD_ABL 0   // timing ablations (results become wrong): 2 rows from an L2-resident window, 4 no stores, 32 no A copies;
                    // forward kernel (profiles/r2_fwd_abl.log): 64 no epilogue work, 128 no MMAs, 512 no correction MMAs,
-                   // 1024 no transform work, 2048 no proxy fence in the epilogue, 4096 no weight copies
+                   // 1024 no transform work, 2048 no proxy fence in the epilogue, 4096 no weight copies;
+                   // 8192 (results stay RIGHT): 3xBF16 without the early refill of the raw-row part of a stage (A/B switch)
 #endif
 
 // Per-role wait-time counters of CTA 0 (build with -DWD_T2_TIMING; read through wd_debug_timing):

@@ -94,6 +94,7 @@ static_assert(T4_LOAD_WARPS * 32 == TC_BM && (T4_XFORM_WARPS == 4 || T4_XFORM_WA
 
 struct T4Barriers {
   uint64_t raw_full[T4_A_STAGES], op_full[T4_A_STAGES], a_empty[T4_A_STAGES];
+  uint64_t x0_free[T4_A_STAGES];    // 3xBF16: the raw-row part of a stage is free again (transform done), see t4_body
   uint64_t b_full[T4_B_SLOTS], b_empty[T4_B_SLOTS];
   uint64_t r_full[T4_R_SLOTS * 2], r_empty[T4_R_SLOTS];    // r_full: one set per epilogue group (t4_rfull below)
   uint64_t tmem_full[3], tmem_empty[3];
@@ -297,6 +298,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
       ptx::mbar_init(&bar->raw_full[s], raw_count);
       ptx::mbar_init(&bar->op_full[s], T4_XFORM_WARPS * (PAIR ? 2 : 1));     // PAIR: both CTAs report to the leader
       ptx::mbar_init(&bar->a_empty[s], 1);
+      ptx::mbar_init(&bar->x0_free[s], T4_XFORM_WARPS);
     }
     for (int s = 0; s < T4_B_SLOTS; ++s) { ptx::mbar_init(&bar->b_full[s], 1); ptx::mbar_init(&bar->b_empty[s], 1); }
     for (int s = 0; s < T4_R_SLOTS; ++s) {
@@ -329,6 +331,11 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
   // lives in slot u % (2 nh) = (stage, half).
   const int nh = W1 > 0 ? 2 : 1, parts = p.split == 1 ? 2 : 1, nslots = B_STAGES * nh;
   const int h1_off = PAIR ? W0 * 64 : W0 * 128;                        // where the second half's unit starts inside a stage
+  // 3xBF16: the MMAs read only the [lo | hi] image (the subtrahend part of the stage); the raw-row part is dead once the
+  // transform warps have read it, so its loads for the stage's NEXT use are issued as soon as the transform is done
+  // (barrier x0_free) instead of after the MMAs of this use (a_empty) -- the gathered rows are the slowest load of the
+  // operand path.  The subtrahend box (GATHER) still waits for a_empty; it is issued by lane 1 of the weight-loader warp.
+  const bool early_x0 = p.split == 2 && (GATHER ? p.x1_tma != 0 : p.a_tma != 0) && !(WD_ABL & 8192);
 
   if (warp >= T4_XFORM_W0 && warp < T4_EPI2_W0) {
     // ================= transform, in place: X0 <- tf32(a), X1 part <- tf32(a - tf32(a)),  a = X0 - act?(X1) =================
@@ -355,11 +362,15 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
       for (int kc = 0; kc < p.KC; ++kc, ++it) {
         const int s = it % T4_A_STAGES;
         T2_WAIT(0, &bar->raw_full[s], (it / T4_A_STAGES) & 1);
+        // early refill, plain operand: nothing but the raw box gates raw_full, so the image part of the stage (still
+        // read by the MMAs of its previous use) is waited for here
+        if (!GATHER && early_x0) T2_WAIT(1, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
         uint8_t* st = ringA + s * T4_A_STAGE + po;
         uint8_t* x1 = ringA + s * T4_A_STAGE + TC_A_STAGE;
         if (WD_ABL & 1024) {      // timing ablation: no transform work
           __syncwarp();
           if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&bar->op_full[s]); else ptx::mbar_arrive(&bar->op_full[s]); }
+          if (lane == 0 && early_x0) ptx::mbar_arrive(&bar->x0_free[s]);
           continue;
         }
         float4 v[T4_XJ], u[T4_XJ];
@@ -400,6 +411,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
         ptx::fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&bar->op_full[s]); else ptx::mbar_arrive(&bar->op_full[s]); }
+        if (lane == 0 && early_x0) ptx::mbar_arrive(&bar->x0_free[s]);   // the raw rows may be refilled while the MMAs run
         const int kcol = kc * TC_BK + c * 4;                             // S goes out after the hand-off to the MMA
         if (keep && kcol < p.lds) {
 #pragma unroll
@@ -436,7 +448,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
         }
         for (int kc = 0; kc < p.KC; ++kc, ++it) {
           const int s = it % T4_A_STAGES;
-          T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+          T2_WAIT(2, early_x0 ? &bar->x0_free[s] : &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
           const int k = kc * TC_BK + c * 4;
           const int rem = (p.K - k) * 4;
           const uint32_t valid = rem >= 16 ? 16u : (rem > 0 ? (uint32_t)rem : 0u);
@@ -444,7 +456,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
           if (WD_ABL & 32) {                        // timing ablation: no operand copies
             if (p.x1_tma && t == 0) ptx::mbar_arrive(&bar->raw_full[s]);
           } else if (p.x1_tma) {                    // subtrahend rows: one TMA box; minuend rows: gathered cp.async
-            if (t == 0) {
+            if (t == 0 && !early_x0) {
               ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)(T4_X1_ROWS * 128));
               ptx::tma_load_2d(ringA + s * T4_A_STAGE + TC_A_STAGE, &p.mx1, kc * TC_BK, (int)row0 - T4_X1_LEAD,
                                &bar->raw_full[s]);
@@ -479,7 +491,7 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
           const int row0 = (int)((tile / p.n_tiles) * TILE_ROWS + rank_rows);
           for (int kc = 0; kc < p.KC; ++kc, ++it) {
             const int s = it % T4_A_STAGES;
-            T2_WAIT(2, &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+            T2_WAIT(2, early_x0 ? &bar->x0_free[s] : &bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
             const bool second = kc >= p.KC0;
             ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)TC_A_STAGE);
             ptx::tma_load_2d(ringA + s * T4_A_STAGE, &p.ma[second ? 1 : 0], (second ? kc - p.KC0 : kc) * TC_BK, row0,
@@ -565,6 +577,18 @@ __device__ __forceinline__ void t4_body(const T4Params& p) {
                             &bar->b_full[slot]);
             }
           }
+        }
+      }
+    } else if (lane == 1 && GATHER && early_x0) {
+      // ================= subtrahend boxes of the early-refill scheme: these still wait for the MMAs (a_empty) =================
+      uint32_t it = 0;
+      for (int64_t tile = t_first; tile < total; tile += t_step) {
+        const int64_t row0 = (tile / p.n_tiles) * TILE_ROWS + rank_rows;
+        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+          const int s = it % T4_A_STAGES;
+          ptx::mbar_wait(&bar->a_empty[s], ((it / T4_A_STAGES) & 1) ^ 1);
+          ptx::mbar_arrive_expect_tx(&bar->raw_full[s], (uint32_t)(T4_X1_ROWS * 128));
+          ptx::tma_load_2d(ringA + s * T4_A_STAGE + TC_A_STAGE, &p.mx1, kc * TC_BK, (int)row0 - T4_X1_LEAD, &bar->raw_full[s]);
         }
       }
     }
