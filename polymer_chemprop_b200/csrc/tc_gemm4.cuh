@@ -46,8 +46,8 @@
 // bf16 of a row) plus two that pair the a_hi half of the operand row with the w_hi half of the weight row (descriptor
 // start addresses 64 bytes apart).  Against 3xTF32: 6 instead of 8 MMAs, half the weight-ring bytes, no hi-image write
 // -- ~28 % fewer bytes through the shared-memory port, which is what bounds this kernel (profiles/r2_fwd_abl.log, L).
-//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader, 6 residual loader, 7-10 operand loaders, 11-14 transform,
-//   15-18 second epilogue group.
+//   warps 0-3 epilogue, 4 MMA issue, 5 weight loader (lane 0; lane 1 issues the subtrahend boxes of the 3xBF16 early-refill
+//   scheme, see early_x0 in t4_body), 6 residual loader, 7-10 operand loaders, 11-14 transform, 15-18 second epilogue group.
 #pragma once
 #include "tc_gemm3.cuh"
 
